@@ -1,0 +1,445 @@
+// fes_core.cuh -- per-trajectory arithmetic of the FES muscle models and their tangent (forward
+// sensitivity) propagation, written once as __host__ __device__ templates.
+//
+// What the reference computes (all paths under the cocofest tree):
+//   S(t)  = sum_i R_i exp(-(t - t_i)/tauc) lambda_i                  models/ding2003.py:230-252
+//   Cn'   = S/tauc - Cn/tauc                                         models/ding2003.py:254-266
+//   F'    = A_eff q - F/(tau1 + tau2 q),  q = Cn/(Km + Cn)           models/ding2003.py:274-311
+//   A_eff = A (1 - exp(-(pw - pd0)/pdt))                             models/ding2007.py:172-188
+//   lambda_i = ar (tanh(bs (I_i - Is)) + cr)                         models/hmed2018.py:169-180
+//   A', Tau1', Km' fatigue rows                                      models/ding2003_with_fatigue.py:197-240
+//   RK1/RK2/RK4 with controls and window constant over an interval   external/bioptim/bioptim/dynamics/integrator.py:300-365
+//
+// How it is computed here (B200-first, not a translation): the window and the controls are constant
+// over an interval, so S(t) factorises as S(t) = E_k * eps(t - t_k) with eps(s) = exp(-s/tauc).  E_k is
+// ONE number per (trajectory, interval), assembled from per-interval window tables (fes_tables kernel);
+// eps at the 2S+1 stage offsets is a table shared by every trajectory and interval.  The inner RK loop
+// therefore contains no exp at all; the two divisions of F' share one reciprocal (MUFU.RCP64H + 5 DFMA,
+// no slow path).  Sensitivities are the exact tangent of the discrete RK map (what casadi's forward AD of
+// the unrolled integrator yields): the nominal stages record the few non-trivial Jacobian entries of F'
+// and every direction column is then pushed through the same four stages; columns are independent, so
+// the compiler interleaves them for ILP.  Structural zeros (Cn decouples from every state, fatigue rows
+// are linear) are removed at compile time through the direction code of each column.
+#pragma once
+
+#include <stdint.h>
+#include <math.h>
+#include <type_traits>
+
+#if defined(__CUDACC__)
+#define FES_HD __host__ __device__ __forceinline__
+#else
+#define FES_HD inline
+#endif
+
+namespace fes {
+
+enum { DING2003 = 0, DING2007 = 1, HMED2018 = 2 };
+enum { G_X0 = 1, G_U = 2, G_P = 4, G_W = 8, G_PF = 16 };
+constexpr int TILE = 5;
+constexpr int NP = 14;
+enum {
+    P_A_REST, P_KM_REST, P_TAU1_REST, P_TAU2, P_ALPHA_A, P_ALPHA_TAU1, P_ALPHA_KM, P_TAU_FAT,
+    P_PD0, P_PDT, P_AR, P_BS, P_IS, P_CR
+};
+
+// direction codes: what a tangent column differentiates with respect to
+enum {
+    D_CN0, D_F0, D_A0, D_TAU10, D_KM0,          // initial state of the interval
+    D_PW, D_INT,                                // controls: pulse width, pulse intensity of a window slot
+    D_WT,                                       // pulse time of a window slot
+    D_A_REST, D_KM_REST, D_TAU1_REST, D_TAU2,   // identifiable parameters (fes_identification_ocp.py:269-299)
+    D_PD0, D_PDT, D_AR, D_BS, D_IS, D_CR,
+    D_ALPHA_A, D_ALPHA_TAU1, D_ALPHA_KM, D_TAU_FAT
+};
+
+template <int KIND, bool FAT, int GROUPS>
+struct Dirs {
+    static constexpr int NX = FAT ? 5 : 2;
+    static constexpr int n_x0 = (GROUPS & G_X0) ? NX : 0;
+    static constexpr int n_u = (GROUPS & G_U) ? (KIND == DING2007 ? 1 : (KIND == HMED2018 ? TILE : 0)) : 0;
+    static constexpr int n_p = (GROUPS & G_P) ? (KIND == DING2003 ? 4 : (KIND == DING2007 ? 6 : 8)) : 0;
+    static constexpr int n_pf = ((GROUPS & G_PF) && FAT) ? 4 : 0;
+    static constexpr int n_w = (GROUPS & G_W) ? TILE : 0;
+    static constexpr int ND = n_x0 + n_u + n_p + n_pf + n_w;
+    // window tables carry per-slot weights (not only their sums)
+    static constexpr bool SLOT = (KIND == HMED2018) || (GROUPS & G_W);
+
+    static constexpr int code(int d) {
+        if (d < n_x0) return D_CN0 + d;
+        d -= n_x0;
+        if (d < n_u) return KIND == DING2007 ? D_PW : D_INT;
+        d -= n_u;
+        if (d < n_p) {
+            if (d < 4) return D_A_REST + d;
+            return KIND == DING2007 ? D_PD0 + (d - 4) : D_AR + (d - 4);
+        }
+        d -= n_p;
+        if (d < n_pf) return D_ALPHA_A + d;
+        return D_WT;
+    }
+    // window-slot index inside the tile for D_INT / D_WT columns
+    static constexpr int slot(int d) {
+        if (d >= n_x0 && d < n_x0 + n_u) return d - n_x0;
+        return d - (n_x0 + n_u + n_p + n_pf);
+    }
+};
+
+constexpr bool dir_has_cn(int c) {
+    return c == D_CN0 || c == D_INT || c == D_WT || c == D_KM_REST || c == D_AR || c == D_BS || c == D_IS || c == D_CR;
+}
+constexpr bool dir_has_dg(int c) { return c == D_PW || c == D_PD0 || c == D_PDT; }
+
+template <int I, int N, class F>
+FES_HD void static_for(F &&f) {
+    if constexpr (I < N) {
+        f(std::integral_constant<int, I>{});
+        static_for<I + 1, N>(f);
+    }
+}
+
+// ---- scalar helpers ---------------------------------------------------------------------------
+FES_HD double xfma(double a, double b, double c) { return fma(a, b, c); }
+FES_HD float xfma(float a, float b, float c) { return fmaf(a, b, c); }
+FES_HD double xexp(double a) { return exp(a); }
+FES_HD float xexp(float a) { return expf(a); }
+FES_HD double xtanh(double a) { return tanh(a); }
+FES_HD float xtanh(float a) { return tanhf(a); }
+
+// reciprocal without the denormal / overflow slow path: the arguments here are products of
+// physiological quantities, (Km + Cn) * (tau1 (Km + Cn) + tau2 Cn), far from the range limits.
+FES_HD double xrcp(double x) {
+#if defined(__CUDA_ARCH__)
+    double r;
+    asm("rcp.approx.ftz.f64 %0, %1;" : "=d"(r) : "d"(x));
+    double e = fma(-x, r, 1.0);
+    e = fma(e, e, e);
+    r = fma(r, e, r);
+    e = fma(-x, r, 1.0);
+    r = fma(r, e, r);
+    return r;
+#else
+    return 1.0 / x;
+#endif
+}
+FES_HD float xrcp(float x) {
+#if defined(__CUDA_ARCH__)
+    float r;
+    asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x));
+    float e = fmaf(-x, r, 1.0f);
+    r = fmaf(r, e, r);
+    return r;
+#else
+    return 1.0f / x;
+#endif
+}
+
+// ---- per-trajectory constants ---------------------------------------------------------------
+template <typename T>
+struct Traj {
+    T a_rest, km_rest, tau1_rest, tau2;
+    T alpha_a, alpha_tau1, alpha_km, kappa, kappa2;  // kappa = 1/tau_fat
+    T a_rest_k, tau1_rest_k, km_rest_k;              // rest value * kappa
+    T r0m1;                                          // r0 - 1 = km_rest + r0_km - 1   (ding2003.py:145-147, :269-271)
+    T pd0, pdt, ar, bs, Is, cr;
+    T inv_tauc;
+};
+
+// p(j) returns canonical parameter j of this trajectory
+template <typename T, class PF>
+FES_HD void load_traj(Traj<T> &tr, PF p, T tauc, T r0_km) {
+    tr.a_rest = p(P_A_REST);
+    tr.km_rest = p(P_KM_REST);
+    tr.tau1_rest = p(P_TAU1_REST);
+    tr.tau2 = p(P_TAU2);
+    tr.alpha_a = p(P_ALPHA_A);
+    tr.alpha_tau1 = p(P_ALPHA_TAU1);
+    tr.alpha_km = p(P_ALPHA_KM);
+    tr.kappa = T(1) / p(P_TAU_FAT);
+    tr.kappa2 = tr.kappa * tr.kappa;
+    tr.a_rest_k = tr.a_rest * tr.kappa;
+    tr.tau1_rest_k = tr.tau1_rest * tr.kappa;
+    tr.km_rest_k = tr.km_rest * tr.kappa;
+    tr.r0m1 = tr.km_rest + r0_km - T(1);
+    tr.pd0 = p(P_PD0);
+    tr.pdt = p(P_PDT);
+    tr.ar = p(P_AR);
+    tr.bs = p(P_BS);
+    tr.Is = p(P_IS);
+    tr.cr = p(P_CR);
+    tr.inv_tauc = T(1) / tauc;
+}
+
+// ---- per-interval quantities ------------------------------------------------------------------
+template <typename T, int ND>
+struct Interval {
+    T E;                       // Cn forcing amplitude: S(t) = E * eps(t - t_k)
+    T g;                       // pulse-width scaling of A (ding2007), 1 otherwise
+    T sE[ND > 0 ? ND : 1];     // d E / d direction
+    T dg[ND > 0 ? ND : 1];     // d g / d direction
+};
+
+// Window table row of one node (fes_tables kernel):  [a, b]  or  [a, b, wa_0..wa_{N-1}, wb_0..wb_{N-1}]
+//   wa_i = exp(-(t_k - t_i)/tauc),  wb_i = exp(-(t_i - t_{i-1})/tauc) wa_i (0 for i = 0),  a = sum wa, b = sum wb
+//   so that  E = sum_i lambda_i (wa_i + (r0 - 1) wb_i)   [= a + (r0 - 1) b when lambda = 1].
+// tab(c) / ctl(c) return element c of this trajectory's row for the current node.
+template <typename T, int KIND, bool FAT, int GROUPS, class TF, class CF>
+FES_HD void interval_setup(const Traj<T> &tr, TF tab, CF ctl, int N, int tile_off,
+                           Interval<T, Dirs<KIND, FAT, GROUPS>::ND> &iv) {
+    using D = Dirs<KIND, FAT, GROUPS>;
+    constexpr int ND = D::ND;
+    static_for<0, ND>([&](auto ic) {
+        constexpr int d = decltype(ic)::value;
+        iv.sE[d] = T(0);
+        iv.dg[d] = T(0);
+    });
+    iv.g = T(1);
+    if constexpr (KIND == DING2007) {
+        // a_calculation, ding2007.py:188; the control is the width of the LAST pulse (ding2007.py:280)
+        const T pw = ctl(0);
+        const T ipdt = T(1) / tr.pdt;
+        const T z = (pw - tr.pd0) * ipdt;
+        const T ew = xexp(-z);
+        iv.g = T(1) - ew;
+        static_for<0, ND>([&](auto ic) {
+            constexpr int d = decltype(ic)::value;
+            constexpr int c = D::code(d);
+            if constexpr (c == D_PW) iv.dg[d] = ew * ipdt;
+            if constexpr (c == D_PD0) iv.dg[d] = -(ew * ipdt);
+            if constexpr (c == D_PDT) iv.dg[d] = -(ew * z * ipdt);
+        });
+    }
+    if constexpr (!D::SLOT) {
+        const T a = tab(0), b = tab(1);
+        iv.E = xfma(tr.r0m1, b, a);
+        static_for<0, ND>([&](auto ic) {
+            constexpr int d = decltype(ic)::value;
+            if constexpr (D::code(d) == D_KM_REST) iv.sE[d] = b;  // d r0 / d km_rest = 1
+        });
+    } else {
+        T E = T(0);
+        for (int i = 0; i < N; ++i) {
+            const T wa = tab(2 + i), wb = tab(2 + N + i);
+            const T W = xfma(tr.r0m1, wb, wa);
+            T lam = T(1), th = T(0), du = T(0);
+            if constexpr (KIND == HMED2018) {
+                du = ctl(i) - tr.Is;
+                th = xtanh(tr.bs * du);          // lambda_i_calculation, hmed2018.py:179
+                lam = tr.ar * (th + tr.cr);
+            }
+            E = xfma(lam, W, E);
+            const T sech2 = T(1) - th * th;
+            static_for<0, ND>([&](auto ic) {
+                constexpr int d = decltype(ic)::value;
+                constexpr int c = D::code(d);
+                if constexpr (c == D_KM_REST) iv.sE[d] = xfma(lam, wb, iv.sE[d]);
+                if constexpr (c == D_AR) iv.sE[d] = xfma(th + tr.cr, W, iv.sE[d]);
+                if constexpr (c == D_BS) iv.sE[d] = xfma(tr.ar * sech2 * du, W, iv.sE[d]);
+                if constexpr (c == D_IS) iv.sE[d] = xfma(-(tr.ar * tr.bs * sech2), W, iv.sE[d]);
+                if constexpr (c == D_CR) iv.sE[d] = xfma(tr.ar, W, iv.sE[d]);
+                if constexpr (c == D_INT) {
+                    if (i == tile_off + D::slot(d)) iv.sE[d] = tr.ar * tr.bs * sech2 * W;
+                }
+                if constexpr (c == D_WT) {
+                    // d E / d t_j = (lambda_j wa_j + (r0 - 1) lambda_{j+1} wb_{j+1}) / tauc
+                    if (i == tile_off + D::slot(d)) iv.sE[d] = xfma(lam * wa, tr.inv_tauc, iv.sE[d]);
+                    if (i == tile_off + D::slot(d) + 1) iv.sE[d] = xfma(tr.r0m1 * lam * wb, tr.inv_tauc, iv.sE[d]);
+                }
+            });
+        }
+        iv.E = E;
+    }
+}
+
+// ---- one RK stage of the nominal trajectory ------------------------------------------------
+template <typename T>
+struct Stage {  // the non-trivial entries of d f / d (x, params) at a stage point
+    T cF, cCn, cKm, cT1, cA, cT2, cG, Fs, dA, dT1, dKm;
+};
+
+template <typename T, int KIND, bool FAT, bool NEED>
+FES_HD void nominal_rhs(const Traj<T> &tr, T Ee, T g, const T *x, T *k, Stage<T> &st) {
+    const T cn = x[0], f = x[1];
+    const T A = FAT ? x[2] : tr.a_rest;
+    const T t1 = FAT ? x[3] : tr.tau1_rest;
+    const T km = FAT ? x[4] : tr.km_rest;
+    k[0] = (Ee - cn) * tr.inv_tauc;
+    const T s = km + cn;
+    const T M = xfma(tr.tau2, cn, t1 * s);  // (tau1 + tau2 q) * s
+    const T r = xrcp(s * M);
+    const T is = r * M;                      // 1 / (Km + Cn)
+    const T invD = s * (r * s);              // 1 / (tau1 + tau2 q)
+    const T q = cn * is;
+    const T Aeff = (KIND == DING2007) ? A * g : A;
+    k[1] = xfma(Aeff, q, -(f * invD));
+    if constexpr (FAT) {
+        k[2] = xfma(tr.alpha_a, f, xfma(-tr.kappa, A, tr.a_rest_k));
+        k[3] = xfma(tr.alpha_tau1, f, xfma(-tr.kappa, t1, tr.tau1_rest_k));
+        k[4] = xfma(tr.alpha_km, f, xfma(-tr.kappa, km, tr.km_rest_k));
+    }
+    if constexpr (NEED) {
+        st.cF = -invD;
+        const T ct1 = f * invD * invD;       // d F' / d tau1
+        st.cT1 = ct1;
+        const T Gc = xfma(ct1, tr.tau2, Aeff);  // d F' / d q
+        const T is2 = is * is;
+        st.cCn = Gc * (km * is2);
+        st.cKm = -(Gc * (cn * is2));
+        st.cA = (KIND == DING2007) ? q * g : q;
+        st.cT2 = ct1 * q;
+        st.cG = A * q;
+        st.Fs = f;
+        if constexpr (FAT) {
+            st.dA = (A - tr.a_rest) * tr.kappa2;   // d/d tau_fat of -(A - A_rest)/tau_fat
+            st.dT1 = (t1 - tr.tau1_rest) * tr.kappa2;
+            st.dKm = (km - tr.km_rest) * tr.kappa2;
+        }
+    }
+}
+
+// ---- one RK stage of one tangent column -----------------------------------------------------
+template <typename T, int KIND, bool FAT, int CODE>
+FES_HD void column_rhs(const Traj<T> &tr, const Stage<T> &st, T eps, T sE, T dg, const T *v, T *k) {
+    constexpr bool CN = dir_has_cn(CODE);
+    if constexpr (CN) {
+        if constexpr (CODE == D_CN0) k[0] = -(v[0] * tr.inv_tauc);
+        else k[0] = xfma(sE, eps, -v[0]) * tr.inv_tauc;
+    } else {
+        k[0] = T(0);
+    }
+    T kf = st.cF * v[1];
+    if constexpr (CN) kf = xfma(st.cCn, v[0], kf);
+    if constexpr (FAT) {
+        kf = xfma(st.cA, v[2], kf);
+        kf = xfma(st.cT1, v[3], kf);
+        kf = xfma(st.cKm, v[4], kf);
+    } else {
+        if constexpr (CODE == D_A_REST) kf += st.cA;
+        if constexpr (CODE == D_TAU1_REST) kf += st.cT1;
+        if constexpr (CODE == D_KM_REST) kf += st.cKm;
+    }
+    if constexpr (CODE == D_TAU2) kf += st.cT2;
+    if constexpr (dir_has_dg(CODE)) kf = xfma(st.cG, dg, kf);
+    k[1] = kf;
+    if constexpr (FAT) {
+        T ka = xfma(tr.alpha_a, v[1], -(tr.kappa * v[2]));
+        T kt = xfma(tr.alpha_tau1, v[1], -(tr.kappa * v[3]));
+        T kk = xfma(tr.alpha_km, v[1], -(tr.kappa * v[4]));
+        if constexpr (CODE == D_A_REST) ka += tr.kappa;
+        if constexpr (CODE == D_TAU1_REST) kt += tr.kappa;
+        if constexpr (CODE == D_KM_REST) kk += tr.kappa;
+        if constexpr (CODE == D_ALPHA_A) ka += st.Fs;
+        if constexpr (CODE == D_ALPHA_TAU1) kt += st.Fs;
+        if constexpr (CODE == D_ALPHA_KM) kk += st.Fs;
+        if constexpr (CODE == D_TAU_FAT) {
+            ka += st.dA;
+            kt += st.dT1;
+            kk += st.dKm;
+        }
+        k[2] = ka;
+        k[3] = kt;
+        k[4] = kk;
+    }
+}
+
+// ---- one RK step (scheme = 1, 2 or 4) of the state and of every tangent column -----------
+// e0, e1, e2 = eps at the step start, midpoint and end (relative to the interval start).
+template <typename T, int KIND, bool FAT, int GROUPS>
+FES_HD void rk_step(const Traj<T> &tr, const Interval<T, Dirs<KIND, FAT, GROUPS>::ND> &iv, int scheme, T h,
+                    T e0, T e1, T e2, T *x, T (*V)[FAT ? 5 : 2]) {
+    using D = Dirs<KIND, FAT, GROUPS>;
+    constexpr int NX = D::NX;
+    constexpr int ND = D::ND;
+    constexpr bool NEED = ND > 0;
+    const T hh = h * T(0.5), h6 = h * T(1.0 / 6.0), h3 = h * T(1.0 / 3.0);
+    Stage<T> st[4];
+    {
+        T k[NX], xs[NX], xn[NX];
+        nominal_rhs<T, KIND, FAT, NEED>(tr, iv.E * e0, iv.g, x, k, st[0]);
+        if (scheme == 1) {
+#pragma unroll
+            for (int j = 0; j < NX; ++j) x[j] = xfma(h, k[j], x[j]);
+        } else {
+#pragma unroll
+            for (int j = 0; j < NX; ++j) {
+                xs[j] = xfma(hh, k[j], x[j]);
+                xn[j] = xfma(h6, k[j], x[j]);
+            }
+            const T Ee1 = iv.E * e1;
+            nominal_rhs<T, KIND, FAT, NEED>(tr, Ee1, iv.g, xs, k, st[1]);
+            if (scheme == 2) {
+#pragma unroll
+                for (int j = 0; j < NX; ++j) x[j] = xfma(h, k[j], x[j]);
+            } else {
+#pragma unroll
+                for (int j = 0; j < NX; ++j) {
+                    xs[j] = xfma(hh, k[j], x[j]);
+                    xn[j] = xfma(h3, k[j], xn[j]);
+                }
+                nominal_rhs<T, KIND, FAT, NEED>(tr, Ee1, iv.g, xs, k, st[2]);
+#pragma unroll
+                for (int j = 0; j < NX; ++j) {
+                    xs[j] = xfma(h, k[j], x[j]);
+                    xn[j] = xfma(h3, k[j], xn[j]);
+                }
+                nominal_rhs<T, KIND, FAT, NEED>(tr, iv.E * e2, iv.g, xs, k, st[3]);
+#pragma unroll
+                for (int j = 0; j < NX; ++j) x[j] = xfma(h6, k[j], xn[j]);
+            }
+        }
+    }
+    static_for<0, ND>([&](auto ic) {
+        constexpr int d = decltype(ic)::value;
+        constexpr int C = D::code(d);
+        // components of this column that can be non-zero: Cn only for the directions that reach it
+        constexpr int J0 = dir_has_cn(C) ? 0 : 1;
+        T *v = V[d];
+        const T sE = iv.sE[d], dg = iv.dg[d];
+        T k[NX], vs[NX], vn[NX];
+        column_rhs<T, KIND, FAT, C>(tr, st[0], e0, sE, dg, v, k);
+        if (scheme == 1) {
+#pragma unroll
+            for (int j = J0; j < NX; ++j) v[j] = xfma(h, k[j], v[j]);
+        } else {
+            vs[0] = T(0);
+#pragma unroll
+            for (int j = J0; j < NX; ++j) {
+                vs[j] = xfma(hh, k[j], v[j]);
+                vn[j] = xfma(h6, k[j], v[j]);
+            }
+            column_rhs<T, KIND, FAT, C>(tr, st[1], e1, sE, dg, vs, k);
+            if (scheme == 2) {
+#pragma unroll
+                for (int j = J0; j < NX; ++j) v[j] = xfma(h, k[j], v[j]);
+            } else {
+#pragma unroll
+                for (int j = J0; j < NX; ++j) {
+                    vs[j] = xfma(hh, k[j], v[j]);
+                    vn[j] = xfma(h3, k[j], vn[j]);
+                }
+                column_rhs<T, KIND, FAT, C>(tr, st[2], e1, sE, dg, vs, k);
+#pragma unroll
+                for (int j = J0; j < NX; ++j) {
+                    vs[j] = xfma(h, k[j], v[j]);
+                    vn[j] = xfma(h3, k[j], vn[j]);
+                }
+                column_rhs<T, KIND, FAT, C>(tr, st[3], e2, sE, dg, vs, k);
+#pragma unroll
+                for (int j = J0; j < NX; ++j) v[j] = xfma(h6, k[j], vn[j]);
+            }
+        }
+    });
+}
+
+// initial value of the tangent columns at the start of an interval (shoot) or of the IVP
+template <typename T, int KIND, bool FAT, int GROUPS>
+FES_HD void init_columns(T (*V)[FAT ? 5 : 2]) {
+    using D = Dirs<KIND, FAT, GROUPS>;
+    static_for<0, D::ND>([&](auto ic) {
+        constexpr int d = decltype(ic)::value;
+#pragma unroll
+        for (int j = 0; j < D::NX; ++j) V[d][j] = (d < D::n_x0 && j == d) ? T(1) : T(0);
+    });
+}
+
+}  // namespace fes

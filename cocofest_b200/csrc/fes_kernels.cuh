@@ -1,0 +1,292 @@
+// fes_kernels.cuh -- sm_100a kernels around fes_core.cuh and their launchers.
+//
+//   fes_tables_kernel  window tables + stage decay table (2N-1 exp per (node[, trajectory]), once per call)
+//   fes_ivp_kernel     one thread per trajectory; single shooting over all nodes
+//                      (replaces bioptim interfaces/solve_ivp_interface.py:56-69)
+//   fes_shoot_kernel   one thread per (scenario, interval); defect + Jacobian columns
+//                      (replaces bioptim limits/penalty.py:1056-1105 + casadi AD)
+//
+// Data layout: structure of arrays, batch index innermost, so every global access of a warp is one
+// coalesced 256-byte (fp64) transaction.  Tables and controls that are shared by all trajectories are
+// staged through shared memory in node chunks (ivp) or read through the read-only path with a
+// warp-uniform address (shoot).  Trajectory state, parameters and all tangent columns live in registers
+// for the whole integration; HBM sees only the initial load, the requested traces and the final store.
+#pragma once
+
+#if defined(__CUDACC__)
+#include <cuda_runtime.h>
+#endif
+
+#include "fes_core.cuh"
+
+namespace fes {
+
+constexpr int BLOCK = 128;
+
+template <typename T>
+struct IvpArgs {
+    const T *params; int64_t pB, pS;   // element j of trajectory b: params[j*pB + b*pS]
+    const T *x0;                       // [nx][B]
+    const T *tab; int64_t tB, tS; int row;  // tables [ns][row]([B]): tab[(n*row + c)*tB + b*tS]
+    const T *eps;                      // [2S+1] stage decay factors
+    const T *ctrl; int64_t cB, cS; int nu;  // [ns][nu]([B])
+    T *x_final, *trace, *sens_final, *sens_trace;
+    int64_t B, trace_B;
+    int trace_mode;                    // 0 none, 1 every RK step, 2 nodes
+    int N, ns, S, scheme, tile_off, chunk;
+    T h, tauc, r0_km;
+};
+
+template <typename T>
+struct ShootArgs {
+    const T *params; int64_t pB, pS;
+    const T *X;                        // [ns+1][nx][B]
+    const T *tab; int64_t tB, tS; int row;
+    const T *eps;
+    const T *ctrl; int64_t cB, cS; int nu;
+    T *G, *Phi, *J;
+    int j_cols, j_col0;
+    int64_t B;
+    int N, ns, S, scheme, tile_off;
+    T h, tauc, r0_km;
+};
+
+#if defined(__CUDACC__)
+
+// ---------------------------------------------------------------------------------------------
+template <typename T>
+__global__ void fes_tables_kernel(const double *__restrict__ win, int64_t wB, int64_t wS, int N, int ns, int row,
+                                  double dt, double t_start, double tauc, T *__restrict__ tab, int64_t tB,
+                                  int S, double h, T *__restrict__ eps) {
+    const int64_t idx = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (idx < 2 * S + 1) eps[idx] = (T)exp(-(0.5 * h * (double)idx) / tauc);
+    if (idx >= (int64_t)ns * tB) return;
+    const int64_t node = idx / tB, b = idx % tB;
+    const double tn = t_start + dt * (double)node;  // optimization_vector.py:373: t_k = dt * k
+    double a = 0.0, bsum = 0.0, prev = 0.0;
+    for (int i = 0; i < N; ++i) {
+        const double ti = win[(node * N + i) * wB + b * wS];
+        const double wa = exp(-(tn - ti) / tauc);                          // exp_time_fun, ding2003.py:213
+        const double wb = (i == 0) ? 0.0 : exp(-(ti - prev) / tauc) * wa;  // (R_i - 1)/(r0 - 1) * wa, ding2003.py:228,249
+        prev = ti;
+        a += wa;
+        bsum += wb;
+        if (row > 2) {
+            tab[(node * row + 2 + i) * tB + b] = (T)wa;
+            tab[(node * row + 2 + N + i) * tB + b] = (T)wb;
+        }
+    }
+    tab[(node * row + 0) * tB + b] = (T)a;
+    tab[(node * row + 1) * tB + b] = (T)bsum;
+}
+
+// ---------------------------------------------------------------------------------------------
+template <typename T, int KIND, bool FAT, int GROUPS>
+__global__ void __launch_bounds__(BLOCK) fes_ivp_kernel(const IvpArgs<T> a) {
+    using D = Dirs<KIND, FAT, GROUPS>;
+    constexpr int NX = D::NX;
+    constexpr int ND = D::ND;
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    T *s_eps = reinterpret_cast<T *>(smem_raw);
+    T *s_tab = s_eps + ((2 * a.S + 1 + 3) & ~3);
+    T *s_ctl = s_tab + (a.tS == 0 ? a.chunk * a.row : 0);
+    const int tid = threadIdx.x;
+    for (int i = tid; i < 2 * a.S + 1; i += BLOCK) s_eps[i] = a.eps[i];
+
+    const int64_t b = (int64_t)blockIdx.x * BLOCK + tid;
+    const bool live = b < a.B;
+    const int64_t bb = live ? b : a.B - 1;  // idle lanes shadow the last trajectory, they store nothing
+
+    Traj<T> tr;
+    load_traj(tr, [&](int j) { return a.params[j * a.pB + bb * a.pS]; }, a.tauc, a.r0_km);
+    T x[NX];
+#pragma unroll
+    for (int j = 0; j < NX; ++j) x[j] = a.x0[j * a.B + bb];
+    T V[ND > 0 ? ND : 1][NX];
+    init_columns<T, KIND, FAT, GROUPS>(V);
+
+    const bool tr_on = live && a.trace_mode != 0 && b < a.trace_B;
+    auto put_state = [&](int64_t pt) {
+        if (a.trace != nullptr) {
+#pragma unroll
+            for (int j = 0; j < NX; ++j) a.trace[(pt * NX + j) * a.trace_B + b] = x[j];
+        }
+    };
+    auto put_sens = [&](int64_t node) {
+        if constexpr (ND > 0) {
+            if (a.sens_trace != nullptr) {
+                static_for<0, ND>([&](auto ic) {
+                    constexpr int d = decltype(ic)::value;
+#pragma unroll
+                    for (int j = 0; j < NX; ++j) a.sens_trace[((node * NX + j) * ND + d) * a.trace_B + b] = V[d][j];
+                });
+            }
+        }
+    };
+    if (tr_on) {
+        put_state(0);
+        put_sens(0);
+    }
+
+    for (int n0 = 0; n0 < a.ns; n0 += a.chunk) {
+        const int nn = min(a.chunk, a.ns - n0);
+        __syncthreads();
+        if (a.tS == 0)
+            for (int i = tid; i < nn * a.row; i += BLOCK) s_tab[i] = a.tab[(int64_t)n0 * a.row + i];
+        if (a.nu > 0 && a.cS == 0)
+            for (int i = tid; i < nn * a.nu; i += BLOCK) s_ctl[i] = a.ctrl[(int64_t)n0 * a.nu + i];
+        __syncthreads();
+        for (int m = 0; m < nn; ++m) {
+            const int node = n0 + m;
+            const T *trow = s_tab + m * a.row;
+            int64_t tstr = 1;
+            if (a.tS != 0) {
+                trow = a.tab + (int64_t)node * a.row * a.tB + bb;
+                tstr = a.tB;
+            }
+            const T *crow = s_ctl + m * a.nu;
+            int64_t cstr = 1;
+            if (a.cS != 0) {
+                crow = a.ctrl + (int64_t)node * a.nu * a.cB + bb;
+                cstr = a.cB;
+            }
+            Interval<T, ND> iv;
+            interval_setup<T, KIND, FAT, GROUPS>(
+                tr, [&](int c) { return trow[c * tstr]; }, [&](int c) { return crow[c * cstr]; }, a.N, a.tile_off, iv);
+            for (int i = 0; i < a.S; ++i) {
+                rk_step<T, KIND, FAT, GROUPS>(tr, iv, a.scheme, a.h, s_eps[2 * i], s_eps[2 * i + 1], s_eps[2 * i + 2], x, V);
+                if (tr_on && a.trace_mode == 1) put_state((int64_t)node * a.S + i + 1);
+            }
+            if (tr_on) {
+                if (a.trace_mode == 2) put_state(node + 1);
+                put_sens(node + 1);
+            }
+        }
+    }
+    if (live) {
+#pragma unroll
+        for (int j = 0; j < NX; ++j) a.x_final[j * a.B + b] = x[j];
+        if constexpr (ND > 0) {
+            if (a.sens_final != nullptr) {
+                static_for<0, ND>([&](auto ic) {
+                    constexpr int d = decltype(ic)::value;
+#pragma unroll
+                    for (int j = 0; j < NX; ++j) a.sens_final[(j * ND + d) * a.B + b] = V[d][j];
+                });
+            }
+        }
+    }
+}
+
+// ---------------------------------------------------------------------------------------------
+template <typename T, int KIND, bool FAT, int GROUPS>
+__global__ void __launch_bounds__(BLOCK) fes_shoot_kernel(const ShootArgs<T> a) {
+    using D = Dirs<KIND, FAT, GROUPS>;
+    constexpr int NX = D::NX;
+    constexpr int ND = D::ND;
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    T *s_eps = reinterpret_cast<T *>(smem_raw);
+    const int tid = threadIdx.x;
+    for (int i = tid; i < 2 * a.S + 1; i += BLOCK) s_eps[i] = a.eps[i];
+    __syncthreads();
+    const int64_t idx = (int64_t)blockIdx.x * BLOCK + tid;
+    if (idx >= a.B * a.ns) return;
+    const int64_t k = idx / a.B, b = idx % a.B;  // batch innermost: a warp shares k when 32 | B
+
+    Traj<T> tr;
+    load_traj(tr, [&](int j) { return __ldg(a.params + j * a.pB + b * a.pS); }, a.tauc, a.r0_km);
+    T x[NX];
+#pragma unroll
+    for (int j = 0; j < NX; ++j) x[j] = __ldg(a.X + (k * NX + j) * a.B + b);
+    T V[ND > 0 ? ND : 1][NX];
+    init_columns<T, KIND, FAT, GROUPS>(V);
+
+    const T *trow = a.tab + k * a.row * a.tB + b * a.tS;
+    const T *crow = a.ctrl + k * a.nu * a.cB + b * a.cS;
+    Interval<T, ND> iv;
+    interval_setup<T, KIND, FAT, GROUPS>(
+        tr, [&](int c) { return __ldg(trow + c * a.tB); }, [&](int c) { return __ldg(crow + c * a.cB); }, a.N,
+        a.tile_off, iv);
+    for (int i = 0; i < a.S; ++i)
+        rk_step<T, KIND, FAT, GROUPS>(tr, iv, a.scheme, a.h, s_eps[2 * i], s_eps[2 * i + 1], s_eps[2 * i + 2], x, V);
+
+#pragma unroll
+    for (int j = 0; j < NX; ++j) {
+        if (a.Phi != nullptr) a.Phi[(k * NX + j) * a.B + b] = x[j];
+        if (a.G != nullptr) a.G[(k * NX + j) * a.B + b] = __ldg(a.X + ((k + 1) * NX + j) * a.B + b) - x[j];
+    }
+    if constexpr (ND > 0) {
+        if (a.J != nullptr) {
+            static_for<0, ND>([&](auto ic) {
+                constexpr int d = decltype(ic)::value;
+#pragma unroll
+                for (int j = 0; j < NX; ++j) a.J[((k * NX + j) * a.j_cols + a.j_col0 + d) * a.B + b] = V[d][j];
+            });
+        }
+    }
+}
+
+// ---------------------------------------------------------------------------------------------
+template <typename T>
+inline size_t ivp_smem_bytes(const IvpArgs<T> &a) {
+    size_t n = (2 * a.S + 1 + 3) & ~3;
+    if (a.tS == 0) n += (size_t)a.chunk * a.row;
+    if (a.nu > 0 && a.cS == 0) n += (size_t)a.chunk * a.nu;
+    return n * sizeof(T);
+}
+
+template <typename T, int KIND, bool FAT, int GROUPS>
+int launch_ivp_t(const IvpArgs<T> &a, cudaStream_t s) {
+    const unsigned grid = (unsigned)((a.B + BLOCK - 1) / BLOCK);
+    fes_ivp_kernel<T, KIND, FAT, GROUPS><<<grid, BLOCK, ivp_smem_bytes(a), s>>>(a);
+    return (int)cudaGetLastError();
+}
+
+template <typename T, int KIND, bool FAT, int GROUPS>
+int launch_shoot_t(const ShootArgs<T> &a, cudaStream_t s) {
+    const int64_t total = a.B * a.ns;
+    const unsigned grid = (unsigned)((total + BLOCK - 1) / BLOCK);
+    const size_t smem = ((2 * a.S + 1 + 3) & ~3) * sizeof(T);
+    fes_shoot_kernel<T, KIND, FAT, GROUPS><<<grid, BLOCK, smem, s>>>(a);
+    return (int)cudaGetLastError();
+}
+
+constexpr int ERR_DIRS = -4;
+
+// one translation unit per (KIND, FAT) instantiates these two for double and float
+template <typename T, int KIND, bool FAT>
+int launch_ivp_kf(int groups, const IvpArgs<T> &a, cudaStream_t s) {
+    switch (groups) {
+        case 0: return launch_ivp_t<T, KIND, FAT, 0>(a, s);
+        case G_X0: return launch_ivp_t<T, KIND, FAT, G_X0>(a, s);
+        case G_P: return launch_ivp_t<T, KIND, FAT, G_P>(a, s);
+        case G_P | G_PF:
+            if constexpr (FAT) return launch_ivp_t<T, KIND, FAT, G_P | G_PF>(a, s);
+            else return ERR_DIRS;
+        default: return ERR_DIRS;
+    }
+}
+
+template <typename T, int KIND, bool FAT>
+int launch_shoot_kf(int groups, const ShootArgs<T> &a, cudaStream_t s) {
+    switch (groups) {
+        case 0: return launch_shoot_t<T, KIND, FAT, 0>(a, s);
+        case G_X0: return launch_shoot_t<T, KIND, FAT, G_X0>(a, s);
+        case G_X0 | G_U:
+            if constexpr (KIND != DING2003) return launch_shoot_t<T, KIND, FAT, G_X0 | G_U>(a, s);
+            else return launch_shoot_t<T, KIND, FAT, G_X0>(a, s);
+        case G_U:
+            if constexpr (KIND != DING2003) return launch_shoot_t<T, KIND, FAT, G_U>(a, s);
+            else return ERR_DIRS;
+        case G_P: return launch_shoot_t<T, KIND, FAT, G_P>(a, s);
+        case G_P | G_PF:
+            if constexpr (FAT) return launch_shoot_t<T, KIND, FAT, G_P | G_PF>(a, s);
+            else return ERR_DIRS;
+        case G_W: return launch_shoot_t<T, KIND, FAT, G_W>(a, s);
+        default: return ERR_DIRS;
+    }
+}
+
+#endif  // __CUDACC__
+
+}  // namespace fes

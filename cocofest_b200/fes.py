@@ -1,0 +1,367 @@
+"""Batched tensor surface of the CUDA integrator (casadi-free primary API).
+
+Layouts are the device library's: structure of arrays, **batch index last** (innermost).
+
+    ivp(...)    single shooting of B independent trajectories over all nodes
+                (what ``IvpFes.integrate`` / bioptim ``solve_ivp_interface.py:56-69`` do one trajectory at a time)
+    shoot(...)  end points, continuity defects and Jacobian blocks of B x ns independent intervals
+                (what bioptim ``penalty.py:1056-1105`` + casadi AD evaluate inside Ipopt)
+
+CUDA tensors are processed in place on the current stream; CPU tensors go through the library's
+host-buffer entry points (H2D -> kernels -> D2H, still computed on the GPU).  There is no CPU path.
+"""
+from __future__ import annotations
+
+import ctypes
+from dataclasses import dataclass
+from fractions import Fraction
+from math import gcd
+
+import numpy as np
+import torch
+
+from . import _lib
+from ._lib import (FES_CTRL_SHARED, FES_DING2003, FES_DING2007, FES_DIR_P, FES_DIR_PF, FES_DIR_U, FES_DIR_W,
+                   FES_DIR_X0, FES_HMED2018, FES_NP, FES_PARAMS_SHARED, FES_TILE, FES_WIN_SHARED, PARAM_INDEX,
+                   PARAM_NAMES, FesDesc, FesIvpBuffers, FesShootBuffers)
+
+PAD_TIME = -10000000  # ding2003.py:396
+PAD_INTENSITY = 50  # hmed2018.py:315
+R0_KM_RELATIONSHIP = 1.04  # ding2003.py:52
+DEFAULT_TAUC = {FES_DING2003: 0.020, FES_DING2007: 0.011, FES_HMED2018: 0.020}  # ding2003.py:51, ding2007.py:71
+
+# identifiable parameters per model kind, in the column order of the FES_DIR_P group
+P_COLUMNS = {
+    FES_DING2003: ("a_rest", "km_rest", "tau1_rest", "tau2"),
+    FES_DING2007: ("a_scale", "km_rest", "tau1_rest", "tau2", "pd0", "pdt"),
+    FES_HMED2018: ("a_rest", "km_rest", "tau1_rest", "tau2", "ar", "bs", "Is", "cr"),
+}
+PF_COLUMNS = ("alpha_a", "alpha_tau1", "alpha_km", "tau_fat")
+
+
+# ---- host-side grid / window logic (numpy; negligible cost) ---------------
+def default_params(kind: int) -> np.ndarray:
+    """Default constants (ding2003.py:51-66, ding2003_with_fatigue.py:50-59, ding2007.py:63-79,
+    hmed2018.py:53-63) in canonical order.  The fatigue constants keep the reference's Python literals
+    ``10e-2`` / ``10e-6`` (they generate the reference's golden vectors)."""
+    p = np.zeros(FES_NP)
+    p[0], p[1], p[2], p[3] = 3009, 0.103, 0.050957, 0.060
+    p[4], p[5], p[6], p[7] = -4.0 * 10e-2, 2.1 * 10e-6, 1.9 * 10e-6, 127
+    p[8], p[9] = 0.000131405, 0.000194138
+    p[10], p[11], p[12], p[13] = 0.586, 0.026, 63.1, 0.833
+    if kind == FES_DING2007:
+        p[0], p[1], p[2], p[3] = 4920, 0.137, 0.060601, 0.001
+    return p
+
+
+def prepare_n_shooting(stim_time, final_time) -> int:
+    """fes_ocp.py:192-222: LCM over pulses of the denominator of t_i / T as limited-denominator fractions."""
+    t_final = Fraction(final_time).limit_denominator()
+    n = 1
+    for t in stim_time:
+        d = (Fraction(t).limit_denominator() / t_final).denominator
+        n = n * d // gcd(n, d)
+    return n
+
+
+def stim_windows(stim_time, n_shooting, final_time, truncation, previous_time=None):
+    """Per-node truncated stimulation windows (ding2003.py:394-429).
+
+    Returns ``(win[ns+1, N] float64, stim_idx_at_node_list)``.  Pulses are assigned to nodes on the
+    node grid (``t_i <= n*dt`` up to 1e-9*dt): the reference's raw float compare drops a pulse at 0.1 from
+    node 1 when dt = 0.3/3, but its golden vectors correspond to the grid-exact assignment.
+    """
+    prev = [] if previous_time is None else list(previous_time)
+    while len(prev) < truncation:
+        prev.insert(0, PAD_TIME)
+    all_stim = np.array(prev + list(stim_time), dtype=np.float64)
+    dt = final_time / n_shooting
+    nodes = np.arange(n_shooting + 1) * dt
+    # last index with all_stim <= node time (+ tolerance); all_stim need not be sorted w.r.t. duplicates
+    hit = all_stim[None, :] - nodes[:, None] <= 1e-9 * dt
+    if not hit.any(axis=1).all():
+        raise ValueError("a node precedes every stimulation of the window (no previous_stim pad?)")
+    node_idx = all_stim.shape[0] - 1 - np.argmax(hit[:, ::-1], axis=1)
+    win = np.stack([all_stim[: i + 1][-truncation:] for i in node_idx])
+    node_list = list(range(n_shooting + 1))
+    stim_idx = [list(node_list[: max(int(i) - truncation + 1, 0)][-truncation:]) for i in node_idx]
+    return win, stim_idx
+
+
+def pulse_mode_times(stim_time, pulse_mode: str):
+    """ivp_fes.py:232-256."""
+    st = list(stim_time)
+    if pulse_mode == "single":
+        return st
+    if pulse_mode == "doublet":
+        st = st + [round(t + 0.005, 3) for t in st]
+    elif pulse_mode == "triplet":
+        st = st + [round(t + 0.005, 3) for t in st] + [round(t + 0.01, 3) for t in st]
+    else:
+        raise ValueError("Pulse mode not yet implemented")
+    st.sort()
+    return st
+
+
+# ---- tensor plumbing ---------------------------------------------------------------------------------
+def _stream_ptr(device) -> int:
+    return torch.cuda.current_stream(device).cuda_stream if device.type == "cuda" else 0
+
+
+def _ptr(t):
+    return None if t is None else ctypes.c_void_p(t.data_ptr())
+
+
+def _prep(t, dtype, device):
+    if t is None:
+        return None
+    t = torch.as_tensor(t)
+    return t.to(device=device, dtype=dtype).contiguous()
+
+
+def _empty(shape, dtype, device):
+    if device.type == "cpu" and torch.cuda.is_available():
+        return torch.empty(shape, dtype=dtype, pin_memory=True)
+    return torch.empty(shape, dtype=dtype, device=device)
+
+
+def _nx(fatigue) -> int:
+    return 5 if fatigue else 2
+
+
+def _nu(kind, N) -> int:
+    return {FES_DING2003: 0, FES_DING2007: 1, FES_HMED2018: N}[kind]
+
+
+def _desc(kind, fatigue, scheme, N, ns, S, dirs, flags, B, dt, t_start, tauc, r0_km, tile_offset=0, trace_every=0,
+          trace_batch=0) -> FesDesc:
+    return FesDesc(_lib.FES_ABI_VERSION, int(kind), int(bool(fatigue)), int(scheme), int(N), int(ns), int(S),
+                   int(dirs), int(flags), int(tile_offset), int(trace_every), 0, int(B), int(trace_batch), float(dt),
+                   float(t_start), float(DEFAULT_TAUC[kind] if tauc is None else tauc), float(r0_km))
+
+
+def _common(kind, fatigue, params, win, ctrl, lead, dtype, N_expected=None):
+    """Normalises params / win / ctrl, derives (device, dtype, B, N, flags)."""
+    lead = torch.as_tensor(lead)
+    device = lead.device
+    if dtype is None:
+        dtype = lead.dtype if lead.dtype in (torch.float32, torch.float64) else torch.float64
+    if dtype not in (torch.float32, torch.float64):
+        raise TypeError("dtype must be torch.float64 or torch.float32")
+    B = lead.shape[-1]
+    flags = 0
+    params = _prep(params, dtype, device)
+    if params.shape[0] != FES_NP:
+        raise ValueError(f"params must have {FES_NP} rows ({', '.join(PARAM_NAMES)})")
+    if params.dim() == 1:
+        flags |= FES_PARAMS_SHARED
+    elif params.shape != (FES_NP, B):
+        raise ValueError(f"params must be [{FES_NP}] or [{FES_NP}, {B}]")
+    win = _prep(win, torch.float64, device)
+    if win.dim() == 2:
+        flags |= FES_WIN_SHARED
+    elif win.dim() != 3 or win.shape[2] != B:
+        raise ValueError("stim window must be [rows, N] or [rows, N, B]")
+    N = win.shape[1]
+    nu = _nu(kind, N)
+    if nu:
+        if ctrl is None:
+            raise ValueError("this model needs controls (last_pulse_width [ns,1] / pulse_intensity [ns,N])")
+        ctrl = _prep(ctrl, dtype, device)
+        if ctrl.dim() == 2:
+            flags |= FES_CTRL_SHARED
+        elif ctrl.dim() != 3 or ctrl.shape[2] != B:
+            raise ValueError("controls must be [ns, nu] or [ns, nu, B]")
+        if ctrl.shape[1] != nu:
+            raise ValueError(f"controls must have {nu} rows per node for this model")
+    else:
+        ctrl = None
+    return device, dtype, B, N, flags, params, win, ctrl
+
+
+@dataclass
+class IvpResult:
+    x_final: torch.Tensor                 # [nx, B]
+    trace: torch.Tensor | None            # [npts, nx, trace_batch]
+    sens_final: torch.Tensor | None       # [nx, nd, B]
+    sens_trace: torch.Tensor | None       # [ns+1, nx, nd, trace_batch]
+    columns: tuple                        # names of the nd sensitivity columns
+    n_shooting: int
+    n_steps: int
+
+
+def direction_columns(kind, fatigue, dirs, N=0, tile_offset=0):
+    """Names of the sensitivity columns the library produces for a direction set."""
+    cols = []
+    if dirs & FES_DIR_X0:
+        cols += ["Cn0", "F0", "A0", "Tau10", "Km0"][: _nx(fatigue)]
+    if dirs & FES_DIR_U:
+        if kind == FES_DING2007:
+            cols += ["last_pulse_width"]
+        elif kind == FES_HMED2018:
+            cols += [f"pulse_intensity_{tile_offset + i}" for i in range(FES_TILE)]
+    if dirs & FES_DIR_P:
+        cols += list(P_COLUMNS[kind])
+        if (dirs & FES_DIR_PF) and fatigue:
+            cols += list(PF_COLUMNS)
+    if dirs & FES_DIR_W:
+        cols += [f"stim_time_{tile_offset + i}" for i in range(FES_TILE)]
+    return tuple(cols)
+
+
+def ivp(kind, fatigue, params, x0, win, dt, n_steps=10, ctrl=None, n_shooting=None, scheme=4, dirs=0, t_start=0.0,
+        tauc=None, r0_km=R0_KM_RELATIONSHIP, trace="none", trace_batch=None, sens_trace=False, dtype=None) -> IvpResult:
+    """Integrates B trajectories over ``n_shooting`` intervals of length ``dt`` with ``n_steps`` RK steps each.
+
+    params [14] | [14,B];  x0 [nx,B];  win [>=ns,N] | [>=ns,N,B] (float64);  ctrl None | [ns,nu] | [ns,nu,B].
+    dirs: 0 | FES_DIR_X0 | FES_DIR_P | FES_DIR_P|FES_DIR_PF  -> chained sensitivities d x(t) / d (x0 | params).
+    trace: "none" | "nodes" (ns+1 points) | "steps" (ns*S+1 points, the IvpFes.integrate layout), for the
+    first ``trace_batch`` trajectories (default: all).
+    """
+    x0 = torch.as_tensor(x0)
+    device, dtype, B, N, flags, params, win, ctrl = _common(kind, fatigue, params, win, ctrl, x0, dtype)
+    nx = _nx(fatigue)
+    x0 = _prep(x0, dtype, device)
+    if x0.shape != (nx, B):
+        raise ValueError(f"x0 must be [{nx}, B]")
+    ns = n_shooting if n_shooting is not None else (ctrl.shape[0] if ctrl is not None else win.shape[0] - 1)
+    if win.shape[0] < ns or (ctrl is not None and ctrl.shape[0] < ns):
+        raise ValueError("stim window / controls have fewer rows than n_shooting")
+    nd = _lib.lib().fes_num_dirs(kind, int(bool(fatigue)), dirs)
+    if nd < 0 or dirs & (FES_DIR_U | FES_DIR_W):
+        raise ValueError("ivp supports dirs in {0, X0, P, P|PF}")
+    modes = {"none": 0, "nodes": n_steps, "steps": 1}
+    if trace not in modes:
+        raise ValueError("trace must be 'none', 'nodes' or 'steps'")
+    want_trace = trace != "none" or sens_trace
+    trace_every = modes[trace] if trace != "none" else (n_steps if sens_trace else 0)
+    tB = (B if trace_batch is None else min(int(trace_batch), B)) if want_trace else 0
+    npts = ns * n_steps + 1 if trace_every == 1 else ns + 1
+    desc = _desc(kind, fatigue, scheme, N, ns, n_steps, dirs, flags, B, dt, t_start, tauc, r0_km,
+                 trace_every=trace_every, trace_batch=tB)
+    out_x = _empty((nx, B), dtype, device)
+    out_tr = _empty((npts, nx, tB), dtype, device) if (trace != "none" and tB) else None
+    out_sf = _empty((nx, nd, B), dtype, device) if nd else None
+    out_st = _empty((ns + 1, nx, nd, tB), dtype, device) if (nd and sens_trace and tB) else None
+    L = _lib.lib()
+    is32 = dtype == torch.float32
+    buf = FesIvpBuffers(_ptr(params), _ptr(x0), _ptr(win), _ptr(ctrl), _ptr(out_x), _ptr(out_tr), _ptr(out_sf),
+                        _ptr(out_st), None, 0)
+    if device.type == "cuda":
+        with torch.cuda.device(device):
+            wbytes = L.fes_workspace_bytes(ctypes.byref(desc), int(is32))
+            ws = torch.empty(max(int(wbytes), 1), dtype=torch.uint8, device=device)
+            buf.workspace, buf.workspace_bytes = ws.data_ptr(), wbytes
+            fn = L.fes_ivp_f32 if is32 else L.fes_ivp_f64
+            _lib.check(fn(ctypes.byref(desc), ctypes.byref(buf), ctypes.c_void_p(_stream_ptr(device))), "fes_ivp")
+            ws.record_stream(torch.cuda.current_stream(device))
+    else:
+        fn = L.fes_ivp_host_f32 if is32 else L.fes_ivp_host_f64
+        _lib.check(fn(ctypes.byref(desc), ctypes.byref(buf), None), "fes_ivp_host")
+    return IvpResult(out_x, out_tr, out_sf, out_st, direction_columns(kind, fatigue, dirs, N), ns, n_steps)
+
+
+@dataclass
+class ShootResult:
+    G: torch.Tensor | None      # [ns, nx, B]   g_k = x_{k+1} - Phi_k
+    Phi: torch.Tensor | None    # [ns, nx, B]
+    Jx: torch.Tensor | None     # [ns, nx, nx, B]      dPhi_k / dx_k
+    Ju: torch.Tensor | None     # [ns, nx, nu, B]      dPhi_k / du_k
+    Jp: torch.Tensor | None     # [ns, nx, np, B]      dPhi_k / d identifiable params (+ fatigue params)
+    Jw: torch.Tensor | None     # [ns, nx, N, B]       dPhi_k / d window pulse times
+    p_columns: tuple
+
+
+def shoot(kind, fatigue, params, X, win, dt, n_steps=10, ctrl=None, scheme=4, want=("x",), t_start=0.0, tauc=None,
+          r0_km=R0_KM_RELATIONSHIP, defects=True, endpoints=False, dtype=None) -> ShootResult:
+    """All intervals of all scenarios at once.
+
+    X [ns+1, nx, B];  params [14] | [14,B];  win [>=ns,N] | [>=ns,N,B];  ctrl None | [ns,nu] | [ns,nu,B].
+    want: subset of {"x", "u", "p", "pf", "w"} selecting the Jacobian blocks.
+    """
+    X = torch.as_tensor(X)
+    device, dtype, B, N, flags, params, win, ctrl = _common(kind, fatigue, params, win, ctrl, X, dtype)
+    nx, nu = _nx(fatigue), _nu(kind, N)
+    X = _prep(X, dtype, device)
+    ns = X.shape[0] - 1
+    if X.dim() != 3 or X.shape[1] != nx or ns < 1:
+        raise ValueError(f"X must be [ns+1, {nx}, B]")
+    if win.shape[0] < ns or (ctrl is not None and ctrl.shape[0] < ns):
+        raise ValueError("stim window / controls have fewer rows than n_shooting")
+    want = set(want)
+    if not want <= {"x", "u", "p", "pf", "w"}:
+        raise ValueError("want must be a subset of {'x','u','p','pf','w'}")
+    if "pf" in want:
+        if not fatigue:
+            raise ValueError("'pf' (fatigue parameters) needs a fatigue model")
+        want.add("p")
+    if nu == 0:
+        want.discard("u")
+    tiles = lambda n: (n + FES_TILE - 1) // FES_TILE
+    cx = nx if "x" in want else 0
+    cu = (1 if kind == FES_DING2007 else tiles(nu) * FES_TILE) if "u" in want else 0
+    np_cols = P_COLUMNS[kind] + (PF_COLUMNS if "pf" in want else ()) if "p" in want else ()
+    cp = len(np_cols)
+    cw = tiles(N) * FES_TILE if "w" in want else 0
+    cols = cx + cu + cp + cw
+    G = _empty((ns, nx, B), dtype, device) if defects else None
+    Phi = _empty((ns, nx, B), dtype, device) if endpoints else None
+    J = _empty((ns, nx, cols, B), dtype, device) if cols else None
+    L = _lib.lib()
+    is32 = dtype == torch.float32
+
+    # passes: (dirs, tile_offset, first column)
+    passes = []
+    if cx and cu:
+        passes.append((FES_DIR_X0 | FES_DIR_U, 0, 0))
+        for t in range(1, tiles(nu) if kind == FES_HMED2018 else 1):
+            passes.append((FES_DIR_U, t * FES_TILE, cx + t * FES_TILE))
+    elif cx:
+        passes.append((FES_DIR_X0, 0, 0))
+    elif cu:
+        for t in range(tiles(nu) if kind == FES_HMED2018 else 1):
+            passes.append((FES_DIR_U, t * FES_TILE, t * FES_TILE))
+    if cp:
+        passes.append((FES_DIR_P | (FES_DIR_PF if "pf" in want else 0), 0, cx + cu))
+    for t in range(tiles(N) if cw else 0):
+        passes.append((FES_DIR_W, t * FES_TILE, cx + cu + cp + t * FES_TILE))
+    if not passes:
+        passes.append((0, 0, 0))
+
+    first = True
+    for dirs, tile_off, col0 in passes:
+        desc = _desc(kind, fatigue, scheme, N, ns, n_steps, dirs, flags, B, dt, t_start, tauc, r0_km, tile_offset=tile_off)
+        buf = FesShootBuffers(_ptr(params), _ptr(X), _ptr(win), _ptr(ctrl), _ptr(G) if first else None,
+                              _ptr(Phi) if first else None, _ptr(J), cols, col0, None, 0)
+        if device.type == "cuda":
+            with torch.cuda.device(device):
+                wbytes = L.fes_workspace_bytes(ctypes.byref(desc), int(is32))
+                ws = torch.empty(max(int(wbytes), 1), dtype=torch.uint8, device=device)
+                buf.workspace, buf.workspace_bytes = ws.data_ptr(), wbytes
+                fn = L.fes_shoot_f32 if is32 else L.fes_shoot_f64
+                _lib.check(fn(ctypes.byref(desc), ctypes.byref(buf), ctypes.c_void_p(_stream_ptr(device))), "fes_shoot")
+                ws.record_stream(torch.cuda.current_stream(device))
+        else:
+            fn = L.fes_shoot_host_f32 if is32 else L.fes_shoot_host_f64
+            _lib.check(fn(ctypes.byref(desc), ctypes.byref(buf), None), "fes_shoot_host")
+        first = False
+
+    o = 0
+    Jx = J[:, :, o:o + cx] if cx else None
+    o += cx
+    Ju = J[:, :, o:o + (nu if cu else 0)] if cu else None
+    o += cu
+    Jp = J[:, :, o:o + cp] if cp else None
+    o += cp
+    Jw = J[:, :, o:o + N] if cw else None
+    return ShootResult(G, Phi, Jx, Ju, Jp, Jw, tuple(np_cols))
+
+
+def probe_fma_peak(is_f32=False, launches=5, device=None) -> float:
+    """Measured FMA throughput of the current GPU in TFLOP/s (2 flop per FMA): the roofline denominator."""
+    out = ctypes.c_double(0.0)
+    dev = torch.device("cuda" if device is None else device)
+    with torch.cuda.device(dev):
+        _lib.check(_lib.lib().fes_probe_fma_peak(int(is_f32), int(launches), ctypes.c_void_p(_stream_ptr(dev)),
+                                                 ctypes.byref(out)), "fes_probe_fma_peak")
+    return out.value

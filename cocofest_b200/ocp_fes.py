@@ -1,0 +1,139 @@
+"""Multiple-shooting side of the path: ``OcpFes.prepare_n_shooting`` and the batched evaluation of the
+continuity defects and their Jacobian that Ipopt consumes.
+
+Reference: cocofest/optimization/fes_ocp.py:192-222 (grid), bioptim limits/penalty.py:1056-1105
+(g_k = x_{k+1} - Phi_k(x_k, u_k, p)), optimization/optimization_vector.py:121-141
+(v = [dt | X_0..X_ns | U_0..U_{ns-1} | P]).  In the reference the defect and its derivatives are a closed
+casadi graph differentiated by AD on every Ipopt iteration; ``FesShooting`` evaluates the same numbers for B
+scenarios x ns intervals in one kernel launch per direction tile and lays the Jacobian out as COO triplets in
+bioptim's variable ordering.  NLP assembly and Ipopt stay on the host, untouched.
+"""
+from __future__ import annotations
+
+import numpy as np
+import torch
+
+from . import fes as _fes
+from ._lib import FES_DING2007, FES_HMED2018
+from .ode_solver import OdeSolver, scheme_and_steps
+
+
+class OcpFes:
+    """Only the static pieces of the reference class that the hot path needs."""
+
+    @staticmethod
+    def prepare_n_shooting(stim_time, final_time):
+        """Number of shooting intervals such that every pulse falls on a node (fes_ocp.py:192-222).
+        Warns like the reference when the grid becomes large."""
+        n_shooting = _fes.prepare_n_shooting(stim_time, final_time)
+        if n_shooting >= 1000:
+            print(f"Warning: The number of shooting nodes is very high n = {n_shooting}.\n"
+                  "The optimization might be long, consider using stimulation time with even spacing (common frequency).")
+        return n_shooting
+
+
+class FesShooting:
+    """Batched multiple-shooting defects and Jacobians of one FES model on a fixed node grid.
+
+    model: a cocofest_b200 model (its ``stim_time`` / ``previous_stim`` define the per-node windows)
+    n_shooting, final_time: the grid (defaults: ``prepare_n_shooting``)
+    ode_solver: OdeSolver.RK1/RK2/RK4 (OcpFes defaults to RK1(10), fes_ocp.py:120; examples pass RK4(10))
+    """
+
+    def __init__(self, model, final_time, n_shooting=None, ode_solver=None, device=None, dtype=torch.float64,
+                 t_start=0.0):
+        self.model = model
+        self.final_time = final_time
+        self.n_shooting = n_shooting if n_shooting is not None else OcpFes.prepare_n_shooting(model.stim_time, final_time)
+        self.dt = final_time / self.n_shooting
+        self.scheme, self.n_steps = scheme_and_steps(ode_solver if ode_solver is not None else OdeSolver.RK1(10))
+        self.device = torch.device(device) if device is not None else torch.device("cuda")
+        self.dtype = dtype
+        self.t_start = t_start
+        data, self.stim_idx_at_node_list = model.get_numerical_data_time_series(self.n_shooting, final_time)
+        self.window = torch.as_tensor(np.ascontiguousarray(data["stim_time"][:, 0, :].T), device=self.device)
+        self.N = self.window.shape[1]
+        self.nx = model.nb_state
+        self.nu = {FES_DING2007: 1, FES_HMED2018: self.N}.get(model.kind, 0)
+
+    # ---- evaluation ------------------------------------------------------------------------------------
+    def _params(self, params):
+        return torch.as_tensor(self.model.param_vector() if params is None else params).to(self.device)
+
+    def evaluate(self, X, U=None, params=None, want=("x", "u"), defects=True, endpoints=False) -> _fes.ShootResult:
+        """X [ns+1, nx, B]; U [ns, nu(, B)]; params None | [14(, B)].  Returns fes.ShootResult."""
+        return _fes.shoot(self.model.kind, self.model.with_fatigue, self._params(params),
+                          torch.as_tensor(X).to(self.device), self.window, self.dt, n_steps=self.n_steps,
+                          ctrl=None if U is None else torch.as_tensor(U).to(self.device), scheme=self.scheme,
+                          want=want, t_start=self.t_start, tauc=self.model.tauc, r0_km=self.model.r0_km_relationship,
+                          defects=defects, endpoints=endpoints, dtype=self.dtype)
+
+    def defects(self, X, U=None, params=None) -> torch.Tensor:
+        """g [ns, nx, B]: the continuity constraint values (penalty.py:1092-1099)."""
+        return self.evaluate(X, U, params, want=()).G
+
+    # ---- Jacobian in bioptim's variable ordering ------------------------------------------------------
+    def variable_layout(self, n_params=0):
+        """Offsets of dt, X, U, P inside bioptim's decision vector (optimization_vector.py:121-141)."""
+        ns, nx, nu = self.n_shooting, self.nx, self.nu
+        off_x = 1
+        off_u = off_x + (ns + 1) * nx
+        off_p = off_u + ns * nu
+        return {"dt": 0, "x": off_x, "u": off_u, "p": off_p, "size": off_p + n_params}
+
+    def jacobian_coo(self, res: _fes.ShootResult):
+        """(rows, cols, vals[nnz, B]) of d g / d v for the continuity rows (row = k*nx + i).
+
+        d g_k/d x_k = -dPhi/dx, d g_k/d x_{k+1} = I, d g_k/d u_k = -dPhi/du, d g_k/d p = -dPhi/dp.  The dt column
+        is not produced: every cocofest FES problem fixes the phase time (fes_ocp.py phase_time=final_time)."""
+        ns, nx, nu = self.n_shooting, self.nx, self.nu
+        n_p = 0 if res.Jp is None else res.Jp.shape[2]
+        lay = self.variable_layout(n_p)
+        k = torch.arange(ns).view(ns, 1, 1)
+        i = torch.arange(nx).view(1, nx, 1)
+        rows, cols, vals = [], [], []
+
+        def add(block, col_of_j):
+            nj = block.shape[2]
+            j = torch.arange(nj).view(1, 1, nj)
+            rows.append((k * nx + i + 0 * j).reshape(-1))
+            cols.append((col_of_j(k, j) + 0 * i).reshape(-1))
+            vals.append(-block.reshape(ns * nx * nj, -1))
+
+        if res.Jx is not None:
+            add(res.Jx, lambda k, j: lay["x"] + k * nx + j)
+        B = res.G.shape[-1] if res.G is not None else res.Jx.shape[-1]
+        rows.append((k * nx + i).reshape(-1))
+        cols.append((lay["x"] + (k + 1) * nx + i).reshape(-1))
+        ref = res.Jx if res.Jx is not None else res.G
+        vals.append(torch.ones((ns * nx, B), dtype=ref.dtype, device=ref.device))
+        if res.Ju is not None:
+            add(res.Ju, lambda k, j: lay["u"] + k * nu + j)
+        if res.Jp is not None:
+            add(res.Jp, lambda k, j: lay["p"] + 0 * k + j)
+        dev = ref.device
+        return torch.cat(rows).to(dev), torch.cat(cols).to(dev), torch.cat(vals, dim=0)
+
+    def jacobian_dense(self, res: _fes.ShootResult, scenario=0) -> torch.Tensor:
+        """Dense [ns*nx, len(v)] Jacobian of one scenario (debug / small problems)."""
+        rows, cols, vals = self.jacobian_coo(res)
+        n_p = 0 if res.Jp is None else res.Jp.shape[2]
+        out = torch.zeros((self.n_shooting * self.nx, self.variable_layout(n_p)["size"]), dtype=vals.dtype, device=vals.device)
+        out[rows, cols] = vals[:, scenario]
+        return out
+
+    # ---- controls helper: the Hmed sliding-window constraint (custom_constraints.py:101-119) ----------
+    def pulse_intensity_controls(self, pulse_intensity, min_intensity=None):
+        """Per-node control vectors consistent with per-pulse intensities: slot j of node k holds the intensity
+        of the pulse at that slot of the node's window; slots before the first pulse get ``min_intensity``
+        (default: the model's min_pulse_intensity, as the reference constraint does)."""
+        lo = self.model.min_pulse_intensity() if min_intensity is None else min_intensity
+        pi = torch.as_tensor(pulse_intensity, dtype=torch.float64)
+        batched = pi.dim() == 2
+        ns, N = self.n_shooting, self.N
+        U = torch.full((ns, N) + ((pi.shape[1],) if batched else ()), float(lo), dtype=torch.float64)
+        for k in range(ns):
+            idx = self.stim_idx_at_node_list[k]
+            for s, src in enumerate(idx):
+                U[k, N - len(idx) + s] = pi[src]
+        return U.to(self.device)

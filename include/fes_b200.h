@@ -1,0 +1,166 @@
+/*
+ * fes_b200.h -- C ABI of the B200-native batched FES muscle-model integrator.
+ *
+ * This is the drop-in boundary for ONE hot path of Ipuch/cocofest: forward integration (plus forward
+ * sensitivities) of the Ding2003 / Ding2007 / Hmed2018 muscle ODEs.  The reference has no FFI for this
+ * path -- it is a closed casadi graph -- so each entry point below names the reference object it replaces
+ * (paths relative to the cocofest tree):
+ *
+ *   fes_ivp_*      replaces the node loop of bioptim's solve_ivp_interface
+ *                  (external/bioptim/bioptim/interfaces/solve_ivp_interface.py:56-69) driving
+ *                  nlp.dynamics[node] (external/bioptim/bioptim/dynamics/integrator.py:82-104, 300-365), as
+ *                  reached from IvpFes.integrate (cocofest/integration/ivp_fes.py:282-297), batched over
+ *                  independent trajectories, optionally with chained forward sensitivities
+ *                  d x(t_n) / d x0 and d x(t_n) / d params.
+ *   fes_shoot_*    replaces the continuity-defect evaluation g_k = x_{k+1} - Phi_k(x_k, u_k, p)
+ *                  (external/bioptim/bioptim/limits/penalty.py:1056-1105) and casadi's AD of it
+ *                  (the Jacobian blocks dPhi/dx_k, dPhi/du_k, dPhi/dp that nlpsol builds in
+ *                  external/bioptim/bioptim/interfaces/interface_utils.py:88-95), batched over
+ *                  (scenario, interval) pairs.
+ *   model arithmetic: cocofest/models/ding2003.py:200-311, ding2003_with_fatigue.py:138-240,
+ *                  ding2007.py:121-188, ding2007_with_fatigue.py:133-241, hmed2018.py:119-180,
+ *                  hmed2018_with_fatigue.py:124-229.
+ *
+ * Conventions
+ *   - every function returns int: 0 = OK, < 0 = invalid argument (fes_strerror), > 0 = cudaError_t.
+ *   - fes_ivp_* / fes_shoot_* take DEVICE pointers owned by the caller; the library allocates nothing
+ *     persistent and keeps no global state; calls are re-entrant; work is enqueued on `stream`
+ *     (a cudaStream_t passed as void*) and NOT synchronised.
+ *   - fes_*_host_* take HOST pointers (pinned for full speed), stage through stream-ordered temporary
+ *     device allocations, and return after the results are in the host buffers.
+ *   - device layout is structure-of-arrays with the BATCH INDEX INNERMOST (coalesced): an array written
+ *     [a][b][B] below stores element (i, j, batch) at ((i*b_dim + j)*B + batch).  "shared" arrays drop
+ *     the batch axis entirely.
+ *   - state order: Cn, F (, A, Tau1, Km)   (nx = 2 without fatigue, 5 with fatigue).
+ */
+#ifndef FES_B200_H
+#define FES_B200_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define FES_ABI_VERSION 1
+
+/* model_kind */
+#define FES_DING2003 0 /* DingModelFrequency[WithFatigue]                (ding2003*.py)  nu = 0 */
+#define FES_DING2007 1 /* DingModelPulseWidthFrequency[WithFatigue]      (ding2007*.py)  nu = 1 */
+#define FES_HMED2018 2 /* DingModelPulseIntensityFrequency[WithFatigue]  (hmed2018*.py)  nu = N */
+
+/* canonical parameter vector, rows of params[FES_NP][B] */
+#define FES_NP 14
+#define FES_P_A_REST 0 /* a_rest; a_scale for FES_DING2007 (ding2007_with_fatigue.py:108,211) */
+#define FES_P_KM_REST 1
+#define FES_P_TAU1_REST 2
+#define FES_P_TAU2 3
+#define FES_P_ALPHA_A 4
+#define FES_P_ALPHA_TAU1 5
+#define FES_P_ALPHA_KM 6
+#define FES_P_TAU_FAT 7
+#define FES_P_PD0 8
+#define FES_P_PDT 9
+#define FES_P_AR 10
+#define FES_P_BS 11
+#define FES_P_IS 12
+#define FES_P_CR 13
+
+/* sensitivity direction groups (FesDesc.dirs is ONE of the supported sets, see fes_num_dirs) */
+#define FES_DIR_X0 1  /* d / d initial state of the interval (nx columns)                                  */
+#define FES_DIR_U 2   /* d / d control: pulse width (1 column) or FES_TILE pulse intensities from tile_offset */
+#define FES_DIR_P 4   /* d / d identifiable parameters: a_rest, km_rest, tau1_rest, tau2 [, pd0, pdt | ar, bs, Is, cr] */
+#define FES_DIR_W 8   /* d / d pulse times of the window: FES_TILE columns from tile_offset                 */
+#define FES_DIR_PF 16 /* with FES_DIR_P, fatigue models: + alpha_a, alpha_tau1, alpha_km, tau_fat          */
+#define FES_TILE 5
+
+/* flags */
+#define FES_PARAMS_SHARED 1 /* params is [FES_NP] instead of [FES_NP][B]                  */
+#define FES_WIN_SHARED 2    /* stim_win is [rows][N] instead of [rows][N][B]              */
+#define FES_CTRL_SHARED 4   /* ctrl is [ns][nu] instead of [ns][nu][B]                    */
+#define FES_TABLES_READY 8  /* workspace already holds the tables of this (desc, stim_win) */
+
+typedef struct FesDesc {
+    int32_t abi_version; /* FES_ABI_VERSION */
+    int32_t model_kind;  /* FES_DING2003 | FES_DING2007 | FES_HMED2018 */
+    int32_t fatigue;     /* 0 | 1 */
+    int32_t scheme;      /* 1 = RK1, 2 = RK2 (midpoint), 4 = RK4  (bioptim integrator.py:324-365) */
+    int32_t n_trunc;     /* N = sum_stim_truncation, window length, 1..64 */
+    int32_t n_shooting;  /* ns = number of intervals */
+    int32_t n_steps;     /* S = RK steps per interval (n_integration_steps), 1..256 */
+    int32_t dirs;        /* sensitivity groups, 0 = none */
+    int32_t flags;
+    int32_t tile_offset; /* first window slot of the FES_DIR_U (hmed) / FES_DIR_W tile */
+    int32_t trace_every; /* ivp only: 0 = no trace, 1 = every RK step (ns*S+1 points), S = nodes (ns+1 points) */
+    int32_t reserved0;
+    int64_t batch;       /* B: trajectories (ivp) or scenarios (shoot) */
+    int64_t trace_batch; /* ivp only: the first trace_batch trajectories are traced */
+    double dt;           /* interval length (final_time / n_shooting) */
+    double t_start;      /* time of node 0 */
+    double tauc;         /* 0.020 (ding2003, hmed2018) / 0.011 (ding2007) */
+    double r0_km;        /* r0_km_relationship = 1.04 (ding2003.py:52) */
+} FesDesc;
+
+/* Buffers of one ivp call.  T = double (_f64) or float (_f32); stim_win is always double. */
+typedef struct FesIvpBuffers {
+    const void *params;     /* [FES_NP][B] | [FES_NP]                                         */
+    const void *x0;         /* [nx][B]                                                        */
+    const double *stim_win; /* [>=ns][N][B] | [>=ns][N]  window of node n = pulses <= t_n, oldest first */
+    const void *ctrl;       /* [ns][nu][B] | [ns][nu] | NULL when nu = 0                      */
+    void *x_final;          /* [nx][B]                                                        */
+    void *trace;            /* [npts][nx][trace_batch] | NULL                                 */
+    void *sens_final;       /* [nx][nd][B] | NULL when dirs = 0                               */
+    void *sens_trace;       /* [ns+1][nx][nd][trace_batch] at nodes | NULL                    */
+    void *workspace;        /* fes_workspace_bytes(desc) bytes of device memory               */
+    int64_t workspace_bytes;
+} FesIvpBuffers;
+
+/* Buffers of one shoot call.  Columns of J follow the group order X0, U, P(+PF), W of desc.dirs. */
+typedef struct FesShootBuffers {
+    const void *params;     /* [FES_NP][B] | [FES_NP]                 */
+    const void *X;          /* [ns+1][nx][B]  decision states at nodes */
+    const double *stim_win; /* [>=ns][N][B] | [>=ns][N]               */
+    const void *ctrl;       /* [ns][nu][B] | [ns][nu] | NULL          */
+    void *G;                /* [ns][nx][B]  g_k = x_{k+1} - Phi_k  | NULL */
+    void *Phi;              /* [ns][nx][B]  end point of every interval | NULL */
+    void *J;                /* [ns][nx][j_cols][B], this call fills columns j_col0 .. j_col0+nd-1 | NULL when dirs = 0 */
+    int32_t j_cols;         /* total number of columns of J */
+    int32_t j_col0;         /* first column written by this call */
+    void *workspace;
+    int64_t workspace_bytes;
+} FesShootBuffers;
+
+int fes_version(void);
+const char *fes_strerror(int code);
+
+/* nx of a model; number of sensitivity columns of a direction set (< 0: unsupported set).
+ * Supported sets: 0, X0, X0|U, U, P, P|PF, W   (ivp: 0, X0, P, P|PF). */
+int fes_num_states(int fatigue);
+int fes_num_controls(int model_kind, int n_trunc);
+int fes_num_dirs(int model_kind, int fatigue, int dirs);
+
+/* device workspace (window tables + stage decay table) needed by a call described by desc */
+int64_t fes_workspace_bytes(const FesDesc *desc, int is_f32);
+
+int fes_ivp_f64(const FesDesc *desc, const FesIvpBuffers *buf, void *stream);
+int fes_ivp_f32(const FesDesc *desc, const FesIvpBuffers *buf, void *stream);
+int fes_shoot_f64(const FesDesc *desc, const FesShootBuffers *buf, void *stream);
+int fes_shoot_f32(const FesDesc *desc, const FesShootBuffers *buf, void *stream);
+
+/* Same calls with HOST buffers (workspace fields ignored): H2D, kernels, D2H, stream synchronised. */
+int fes_ivp_host_f64(const FesDesc *desc, const FesIvpBuffers *host_buf, void *stream);
+int fes_ivp_host_f32(const FesDesc *desc, const FesIvpBuffers *host_buf, void *stream);
+int fes_shoot_host_f64(const FesDesc *desc, const FesShootBuffers *host_buf, void *stream);
+int fes_shoot_host_f32(const FesDesc *desc, const FesShootBuffers *host_buf, void *stream);
+
+/* Roofline denominators measured on the device the caller made current: runs `launches` launches of a
+ * register-only FMA kernel on `stream` and returns the best FMA-flop rate (2 flop per FMA) in TFLOP/s. */
+int fes_probe_fma_peak(int is_f32, int launches, void *stream, double *tflops_out);
+
+/* Kernel launches issued by this library in the calling process since load (for bench accounting). */
+int64_t fes_launch_count(void);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* FES_B200_H */

@@ -1,0 +1,247 @@
+// fes_emul.cpp -- HOST BUILD OF THE KERNEL ARITHMETIC, TEST INFRASTRUCTURE ONLY.
+//
+// The build container has no GPU.  To let the CPU-only CI exercise the same templates the CUDA kernels
+// are made of (cocofest_b200/csrc/fes_core.cuh: interval_setup, rk_step, the tangent columns) and the
+// same argument checks / workspace carving (fes_abi_common.hpp), this file compiles them with g++ and
+// drives them with plain loops over (trajectory, node), exporting the fes_* symbols of
+// include/fes_b200.h with HOST pointers.  Nothing under cocofest_b200/ references this library; only
+// tests/ load it, explicitly, through the `emul_lib` fixture.  It is not a product CPU path.
+#include <cmath>
+#include <cstdint>
+#include <vector>
+
+#include "fes_abi_common.hpp"
+
+using namespace fes;
+using namespace fes::abi;
+
+namespace {
+
+template <typename T>
+void tables_cpu(const FesDesc *d, const double *win, const Carve &c, void *ws) {
+    T *eps = reinterpret_cast<T *>((char *)ws + c.eps_off);
+    T *tab = reinterpret_cast<T *>((char *)ws + c.tab_off);
+    const int S = d->n_steps, N = d->n_trunc, ns = d->n_shooting, row = c.row;
+    const double h = d->dt / S, tauc = d->tauc;
+    const int64_t tB = c.tB;
+    const int64_t wB = (d->flags & FES_WIN_SHARED) ? 1 : d->batch, wS = (d->flags & FES_WIN_SHARED) ? 0 : 1;
+    for (int i = 0; i < 2 * S + 1; ++i) eps[i] = (T)std::exp(-(0.5 * h * (double)i) / tauc);
+    for (int64_t node = 0; node < ns; ++node)
+        for (int64_t b = 0; b < tB; ++b) {
+            const double tn = d->t_start + d->dt * (double)node;
+            double a = 0.0, bsum = 0.0, prev = 0.0;
+            for (int i = 0; i < N; ++i) {
+                const double ti = win[(node * N + i) * wB + b * wS];
+                const double wa = std::exp(-(tn - ti) / tauc);
+                const double wb = (i == 0) ? 0.0 : std::exp(-(ti - prev) / tauc) * wa;
+                prev = ti;
+                a += wa;
+                bsum += wb;
+                if (row > 2) {
+                    tab[(node * row + 2 + i) * tB + b] = (T)wa;
+                    tab[(node * row + 2 + N + i) * tB + b] = (T)wb;
+                }
+            }
+            tab[(node * row + 0) * tB + b] = (T)a;
+            tab[(node * row + 1) * tB + b] = (T)bsum;
+        }
+}
+
+template <typename T, int KIND, bool FAT, int GROUPS>
+int ivp_cpu(const IvpArgs<T> &a) {
+    using D = Dirs<KIND, FAT, GROUPS>;
+    constexpr int NX = D::NX, ND = D::ND;
+    for (int64_t b = 0; b < a.B; ++b) {
+        Traj<T> tr;
+        load_traj(tr, [&](int j) { return a.params[j * a.pB + b * a.pS]; }, a.tauc, a.r0_km);
+        T x[NX];
+        for (int j = 0; j < NX; ++j) x[j] = a.x0[j * a.B + b];
+        T V[ND > 0 ? ND : 1][NX];
+        init_columns<T, KIND, FAT, GROUPS>(V);
+        const bool tr_on = a.trace_mode != 0 && b < a.trace_B;
+        auto put_state = [&](int64_t pt) {
+            if (a.trace) for (int j = 0; j < NX; ++j) a.trace[(pt * NX + j) * a.trace_B + b] = x[j];
+        };
+        auto put_sens = [&](int64_t node) {
+            if (ND > 0 && a.sens_trace)
+                for (int d = 0; d < ND; ++d)
+                    for (int j = 0; j < NX; ++j) a.sens_trace[((node * NX + j) * ND + d) * a.trace_B + b] = V[d][j];
+        };
+        if (tr_on) { put_state(0); put_sens(0); }
+        for (int node = 0; node < a.ns; ++node) {
+            const T *trow = a.tab + (int64_t)node * a.row * a.tB + b * a.tS;
+            const T *crow = a.ctrl + (int64_t)node * a.nu * a.cB + b * a.cS;
+            Interval<T, ND> iv;
+            interval_setup<T, KIND, FAT, GROUPS>(
+                tr, [&](int c) { return trow[c * a.tB]; }, [&](int c) { return crow[c * a.cB]; }, a.N, a.tile_off, iv);
+            for (int i = 0; i < a.S; ++i) {
+                rk_step<T, KIND, FAT, GROUPS>(tr, iv, a.scheme, a.h, a.eps[2 * i], a.eps[2 * i + 1], a.eps[2 * i + 2], x, V);
+                if (tr_on && a.trace_mode == 1) put_state((int64_t)node * a.S + i + 1);
+            }
+            if (tr_on) {
+                if (a.trace_mode == 2) put_state(node + 1);
+                put_sens(node + 1);
+            }
+        }
+        for (int j = 0; j < NX; ++j) a.x_final[j * a.B + b] = x[j];
+        if (ND > 0 && a.sens_final)
+            for (int d = 0; d < ND; ++d)
+                for (int j = 0; j < NX; ++j) a.sens_final[(j * ND + d) * a.B + b] = V[d][j];
+    }
+    return 0;
+}
+
+template <typename T, int KIND, bool FAT, int GROUPS>
+int shoot_cpu(const ShootArgs<T> &a) {
+    using D = Dirs<KIND, FAT, GROUPS>;
+    constexpr int NX = D::NX, ND = D::ND;
+    for (int64_t k = 0; k < a.ns; ++k)
+        for (int64_t b = 0; b < a.B; ++b) {
+            Traj<T> tr;
+            load_traj(tr, [&](int j) { return a.params[j * a.pB + b * a.pS]; }, a.tauc, a.r0_km);
+            T x[NX];
+            for (int j = 0; j < NX; ++j) x[j] = a.X[(k * NX + j) * a.B + b];
+            T V[ND > 0 ? ND : 1][NX];
+            init_columns<T, KIND, FAT, GROUPS>(V);
+            const T *trow = a.tab + k * a.row * a.tB + b * a.tS;
+            const T *crow = a.ctrl + k * a.nu * a.cB + b * a.cS;
+            Interval<T, ND> iv;
+            interval_setup<T, KIND, FAT, GROUPS>(
+                tr, [&](int c) { return trow[c * a.tB]; }, [&](int c) { return crow[c * a.cB]; }, a.N, a.tile_off, iv);
+            for (int i = 0; i < a.S; ++i)
+                rk_step<T, KIND, FAT, GROUPS>(tr, iv, a.scheme, a.h, a.eps[2 * i], a.eps[2 * i + 1], a.eps[2 * i + 2], x, V);
+            for (int j = 0; j < NX; ++j) {
+                if (a.Phi) a.Phi[(k * NX + j) * a.B + b] = x[j];
+                if (a.G) a.G[(k * NX + j) * a.B + b] = a.X[((k + 1) * NX + j) * a.B + b] - x[j];
+            }
+            if (ND > 0 && a.J)
+                for (int d = 0; d < ND; ++d)
+                    for (int j = 0; j < NX; ++j) a.J[((k * NX + j) * a.j_cols + a.j_col0 + d) * a.B + b] = V[d][j];
+        }
+    return 0;
+}
+
+template <typename T, int KIND, bool FAT>
+int ivp_kf(int groups, const IvpArgs<T> &a) {
+    switch (groups) {
+        case 0: return ivp_cpu<T, KIND, FAT, 0>(a);
+        case G_X0: return ivp_cpu<T, KIND, FAT, G_X0>(a);
+        case G_P: return ivp_cpu<T, KIND, FAT, G_P>(a);
+        case G_P | G_PF:
+            if constexpr (FAT) return ivp_cpu<T, KIND, FAT, G_P | G_PF>(a);
+            else return E_DIRS;
+    }
+    return E_DIRS;
+}
+template <typename T, int KIND, bool FAT>
+int shoot_kf(int groups, const ShootArgs<T> &a) {
+    switch (groups) {
+        case 0: return shoot_cpu<T, KIND, FAT, 0>(a);
+        case G_X0: return shoot_cpu<T, KIND, FAT, G_X0>(a);
+        case G_X0 | G_U:
+            if constexpr (KIND != DING2003) return shoot_cpu<T, KIND, FAT, G_X0 | G_U>(a);
+            else return shoot_cpu<T, KIND, FAT, G_X0>(a);
+        case G_U:
+            if constexpr (KIND != DING2003) return shoot_cpu<T, KIND, FAT, G_U>(a);
+            else return E_DIRS;
+        case G_P: return shoot_cpu<T, KIND, FAT, G_P>(a);
+        case G_P | G_PF:
+            if constexpr (FAT) return shoot_cpu<T, KIND, FAT, G_P | G_PF>(a);
+            else return E_DIRS;
+        case G_W: return shoot_cpu<T, KIND, FAT, G_W>(a);
+    }
+    return E_DIRS;
+}
+#define KF_SWITCH(fn, ...)                                    \
+    switch (kind * 2 + fat) {                                 \
+        case 0: return fn<T, 0, false>(__VA_ARGS__);          \
+        case 1: return fn<T, 0, true>(__VA_ARGS__);           \
+        case 2: return fn<T, 1, false>(__VA_ARGS__);          \
+        case 3: return fn<T, 1, true>(__VA_ARGS__);           \
+        case 4: return fn<T, 2, false>(__VA_ARGS__);          \
+        case 5: return fn<T, 2, true>(__VA_ARGS__);           \
+    }                                                         \
+    return E_MODEL;
+template <typename T> int disp_ivp(int kind, int fat, int groups, const IvpArgs<T> &a) { KF_SWITCH(ivp_kf, groups, a) }
+template <typename T> int disp_shoot(int kind, int fat, int groups, const ShootArgs<T> &a) { KF_SWITCH(shoot_kf, groups, a) }
+
+template <typename T>
+int ivp_impl(const FesDesc *d, const FesIvpBuffers *b) {
+    int rc = check_desc(d, true);
+    if (rc) return rc;
+    if (!b || !b->params || !b->x0 || !b->x_final) return E_BUF;
+    if (num_controls(d->model_kind, d->n_trunc) > 0 && !b->ctrl) return E_BUF;
+    if (d->trace_every != 0 && d->trace_batch > 0 && !b->trace && !b->sens_trace) return E_TRACE;
+    const Carve c = carve(d, sizeof(T));
+    if (!b->workspace || b->workspace_bytes < (int64_t)c.total) return E_WORKSPACE;
+    if (!(d->flags & FES_TABLES_READY)) {
+        if (!b->stim_win) return E_BUF;
+        tables_cpu<T>(d, b->stim_win, c, b->workspace);
+    }
+    IvpArgs<T> a;
+    fill_ivp_args<T>(d, b, c, a);
+    return disp_ivp<T>(d->model_kind, d->fatigue, d->dirs, a);
+}
+template <typename T>
+int shoot_impl(const FesDesc *d, const FesShootBuffers *b) {
+    int rc = check_desc(d, false);
+    if (rc) return rc;
+    if (!b || !b->params || !b->X) return E_BUF;
+    if (num_controls(d->model_kind, d->n_trunc) > 0 && !b->ctrl) return E_BUF;
+    int groups = d->dirs;
+    if (d->model_kind == FES_DING2003) groups &= ~FES_DIR_U;
+    const int nd = num_dirs(d->model_kind, d->fatigue, groups);
+    if (nd > 0 && b->J && (b->j_col0 < 0 || b->j_col0 + nd > b->j_cols)) return E_SIZE;
+    const Carve c = carve(d, sizeof(T));
+    if (!b->workspace || b->workspace_bytes < (int64_t)c.total) return E_WORKSPACE;
+    if (!(d->flags & FES_TABLES_READY)) {
+        if (!b->stim_win) return E_BUF;
+        tables_cpu<T>(d, b->stim_win, c, b->workspace);
+    }
+    ShootArgs<T> a;
+    fill_shoot_args<T>(d, b, c, a);
+    return disp_shoot<T>(d->model_kind, d->fatigue, groups, a);
+}
+}  // namespace
+
+extern "C" {
+int fes_version(void) { return FES_ABI_VERSION; }
+const char *fes_strerror(int code) { const char *m = strerror_abi(code); return m ? m : "unknown error"; }
+int fes_num_states(int fatigue) { return fatigue ? 5 : 2; }
+int fes_num_controls(int k, int n) { return num_controls(k, n); }
+int fes_num_dirs(int k, int f, int dirs) {
+    if (k < 0 || k > 2) return -1;
+    if (k == FES_DING2003 && dirs == (FES_DIR_X0 | FES_DIR_U)) dirs = FES_DIR_X0;
+    return num_dirs(k, f ? 1 : 0, dirs);
+}
+int64_t fes_workspace_bytes(const FesDesc *d, int is_f32) {
+    if (!d || d->n_steps < 1 || d->n_shooting < 1 || d->n_trunc < 1 || d->batch < 1) return -1;
+    return (int64_t)carve(d, is_f32 ? 4 : 8).total;
+}
+int fes_ivp_f64(const FesDesc *d, const FesIvpBuffers *b, void *) { return ivp_impl<double>(d, b); }
+int fes_ivp_f32(const FesDesc *d, const FesIvpBuffers *b, void *) { return ivp_impl<float>(d, b); }
+int fes_shoot_f64(const FesDesc *d, const FesShootBuffers *b, void *) { return shoot_impl<double>(d, b); }
+int fes_shoot_f32(const FesDesc *d, const FesShootBuffers *b, void *) { return shoot_impl<float>(d, b); }
+
+// host-buffer entry points: same loops, workspace allocated here
+#define HOST_VARIANT(name, impl, T, Buf)                                                      \
+    int name(const FesDesc *d, const Buf *b, void *) {                                        \
+        if (!d || !b) return E_DESC;                                                          \
+        FesDesc dd = *d;                                                                      \
+        dd.flags &= ~FES_TABLES_READY;                                                        \
+        const int64_t wb = fes_workspace_bytes(&dd, sizeof(T) == 4);                          \
+        if (wb < 0) return E_SIZE;                                                            \
+        std::vector<char> ws((size_t)wb + 16);                                                \
+        Buf bb = *b;                                                                          \
+        bb.workspace = ws.data();                                                             \
+        bb.workspace_bytes = wb;                                                              \
+        return impl<T>(&dd, &bb);                                                             \
+    }
+HOST_VARIANT(fes_ivp_host_f64, ivp_impl, double, FesIvpBuffers)
+HOST_VARIANT(fes_ivp_host_f32, ivp_impl, float, FesIvpBuffers)
+HOST_VARIANT(fes_shoot_host_f64, shoot_impl, double, FesShootBuffers)
+HOST_VARIANT(fes_shoot_host_f32, shoot_impl, float, FesShootBuffers)
+int fes_probe_fma_peak(int, int, void *, double *) { return E_DESC; }
+int64_t fes_launch_count(void) { return 0; }
+int fes_is_host_emulation(void) { return 1; }
+}

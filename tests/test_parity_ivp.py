@@ -1,0 +1,187 @@
+"""Parity of the kernel arithmetic against the oracle: batched IVP (forward map + chained sensitivities).
+
+Every test runs twice: `emul` (host build of the kernel source, CPU CI) and `cuda` (the product, -m gpu).
+Tolerance: 1e-9 relative in fp64 (BASELINE.json north_star), 1e-4 in fp32."""
+import json
+from pathlib import Path
+
+import numpy as np
+import pytest
+import torch
+
+from cocofest_b200 import fes
+from oracle import fes_oracle as fo
+from oracle import fes_oracle_c as foc
+from tests.conftest import BACKENDS
+from tests.problems import MODELS, P_COLS, PF_COLS, oracle_win, random_problem, rel_err, to_lib
+
+GOLD = json.loads((Path(__file__).parent / "golden" / "ivp_golden.json").read_text())
+RTOL64 = 1e-9
+RTOL32 = 1e-4
+
+
+def _golden_inputs(name, device, pulse_mode="single", stim=(0, 0.1, 0.2)):
+    kind, fat = MODELS[name]
+    st = fes.pulse_mode_times(list(stim), pulse_mode)
+    ns = fes.prepare_n_shooting(st, 0.3)
+    win, idx = fes.stim_windows(st, ns, 0.3, 3)
+    p = fes.default_params(kind)
+    ctrl = None
+    if kind == fo.DING2007:
+        ctrl = torch.tensor(fo.ivp_controls_pulse_width(GOLD["pulse_width"], idx, ns), device=device)
+    if kind == fo.HMED2018:
+        ctrl = torch.tensor(fo.ivp_controls_pulse_intensity(GOLD["pulse_intensity"], idx, ns, 3), device=device)
+    x0 = torch.tensor(fo.rest_state(kind, fat, p), device=device)[:, None]
+    return kind, fat, torch.tensor(p, device=device), x0, torch.tensor(win, device=device), ctrl, ns
+
+
+@pytest.mark.parametrize("backend", BACKENDS, indirect=True)
+@pytest.mark.parametrize("name", list(MODELS))
+def test_reference_golden_force_trajectories(backend, name):
+    """The six 31-point force vectors of reference tests/shard1/test_ivp.py:28-124."""
+    kind, fat, p, x0, win, ctrl, ns = _golden_inputs(name, backend)
+    res = fes.ivp(kind, fat, p, x0, win, 0.3 / ns, n_steps=10, ctrl=ctrl, n_shooting=ns, trace="steps")
+    F = res.trace[:, 1, 0].cpu().numpy()
+    np.testing.assert_almost_equal(F, np.array(GOLD["F"][name]), decimal=GOLD["decimal"])
+
+
+@pytest.mark.parametrize("backend", BACKENDS, indirect=True)
+def test_reference_golden_pulse_modes(backend):
+    """Doublet and (state-leaked) triplet slices of test_ivp.py:127-169."""
+    name = "ding2003_with_fatigue"
+    kind, fat, p, x0, win, ctrl, ns = _golden_inputs(name, backend, "doublet")
+    assert ns == 60
+    res = fes.ivp(kind, fat, p, x0, win, 0.3 / ns, n_steps=10, n_shooting=ns, trace="steps")
+    np.testing.assert_almost_equal(res.trace[150:180, 1, 0].cpu().numpy(),
+                                   np.array(GOLD["F"]["pulse_mode_doublet_150_180"]), decimal=7)
+    leaked = fes.pulse_mode_times(fes.pulse_mode_times([0, 0.1, 0.2], "doublet"), "triplet")
+    kind, fat, p, x0, win, ctrl, ns = _golden_inputs(name, backend, "single", stim=leaked)
+    res = fes.ivp(kind, fat, p, x0, win, 0.3 / ns, n_steps=10, n_shooting=ns, trace="steps")
+    np.testing.assert_almost_equal(res.trace[350:380, 1, 0].cpu().numpy(),
+                                   np.array(GOLD["F"]["pulse_mode_triplet_350_380"]), decimal=7)
+
+
+@pytest.mark.parametrize("backend", BACKENDS, indirect=True)
+@pytest.mark.parametrize("name", list(MODELS))
+@pytest.mark.parametrize("scheme", [1, 2, 4])
+def test_ivp_forward_matches_oracle(backend, name, scheme):
+    pb = random_problem(name, B=37, seed=11, shared_ctrl=False)
+    S = 5
+    params, x0, win, ctrl = to_lib(pb, backend)
+    res = fes.ivp(pb["kind"], pb["fat"], params, x0, win, pb["dt"], n_steps=S, ctrl=ctrl, n_shooting=pb["ns"],
+                  scheme=scheme, trace="steps", trace_batch=5)
+    ref = foc.ivp(pb["kind"], pb["fat"], scheme, pb["N"], pb["ns"], S, pb["dt"], pb["tauc"], fo.R0_KM_RELATIONSHIP,
+                  pb["params"], pb["x0"], oracle_win(pb), pb["u"], trace_B=5, trace_every=1)
+    assert rel_err(res.x_final.cpu().numpy().T, ref["final"]) < RTOL64
+    got = np.transpose(res.trace.cpu().numpy(), (2, 0, 1))  # [tB, npts, nx]
+    assert rel_err(got, ref["trace"]) < RTOL64
+    # node traces are the sub-step trace sampled every S points
+    res_n = fes.ivp(pb["kind"], pb["fat"], params, x0, win, pb["dt"], n_steps=S, ctrl=ctrl, n_shooting=pb["ns"],
+                    scheme=scheme, trace="nodes")
+    assert torch.equal(res_n.trace[:, :, :5], res.trace[::S])
+    assert torch.equal(res_n.x_final, res.x_final)
+
+
+@pytest.mark.parametrize("backend", BACKENDS, indirect=True)
+@pytest.mark.parametrize("name", list(MODELS))
+def test_ivp_per_trajectory_windows_and_shared_params(backend, name):
+    pb = random_problem(name, B=19, seed=5, shared_params=True, per_traj_win=True)
+    params, x0, win, ctrl = to_lib(pb, backend)
+    res = fes.ivp(pb["kind"], pb["fat"], params, x0, win, pb["dt"], n_steps=4, ctrl=ctrl, n_shooting=pb["ns"])
+    ref = foc.ivp(pb["kind"], pb["fat"], 4, pb["N"], pb["ns"], 4, pb["dt"], pb["tauc"], fo.R0_KM_RELATIONSHIP,
+                  pb["params"], pb["x0"], oracle_win(pb), pb["u"])
+    assert rel_err(res.x_final.cpu().numpy().T, ref["final"]) < RTOL64
+
+
+@pytest.mark.parametrize("backend", BACKENDS, indirect=True)
+@pytest.mark.parametrize("name", list(MODELS))
+def test_ivp_sensitivities_wrt_x0_match_oracle(backend, name):
+    pb = random_problem(name, B=21, seed=3)
+    S = 6
+    params, x0, win, ctrl = to_lib(pb, backend)
+    res = fes.ivp(pb["kind"], pb["fat"], params, x0, win, pb["dt"], n_steps=S, ctrl=ctrl, n_shooting=pb["ns"],
+                  dirs=fes.FES_DIR_X0, sens_trace=True, trace="nodes", trace_batch=4)
+    ref = foc.ivp(pb["kind"], pb["fat"], 4, pb["N"], pb["ns"], S, pb["dt"], pb["tauc"], fo.R0_KM_RELATIONSHIP,
+                  pb["params"], pb["x0"], oracle_win(pb), pb["u"], seed_x0=True, trace_B=4, sens_trace=True)
+    assert rel_err(res.x_final.cpu().numpy().T, ref["final"]) < RTOL64
+    got = np.transpose(res.sens_final.cpu().numpy(), (2, 0, 1))  # [B, nx, nd]
+    assert rel_err(got, ref["sens_final"]) < RTOL64
+    got_t = np.transpose(res.sens_trace.cpu().numpy(), (3, 0, 1, 2))  # [tB, ns+1, nx, nd]
+    assert rel_err(got_t, ref["sens_trace"]) < RTOL64
+    assert len(res.columns) == pb["nx"]
+
+
+@pytest.mark.parametrize("backend", BACKENDS, indirect=True)
+@pytest.mark.parametrize("name", list(MODELS))
+@pytest.mark.parametrize("with_pf", [False, True])
+def test_ivp_sensitivities_wrt_parameters_match_oracle(backend, name, with_pf):
+    pb = random_problem(name, B=13, seed=9, shared_ctrl=False)
+    if with_pf and not pb["fat"]:
+        pytest.skip("fatigue parameters only exist on fatigue models")
+    S = 5
+    params, x0, win, ctrl = to_lib(pb, backend)
+    dirs = fes.FES_DIR_P | (fes.FES_DIR_PF if with_pf else 0)
+    res = fes.ivp(pb["kind"], pb["fat"], params, x0, win, pb["dt"], n_steps=S, ctrl=ctrl, n_shooting=pb["ns"], dirs=dirs)
+    pdir = P_COLS[pb["kind"]] + (PF_COLS if with_pf else [])
+    ref = foc.ivp(pb["kind"], pb["fat"], 4, pb["N"], pb["ns"], S, pb["dt"], pb["tauc"], fo.R0_KM_RELATIONSHIP,
+                  pb["params"], pb["x0"], oracle_win(pb), pb["u"], pdir=pdir)
+    got = np.transpose(res.sens_final.cpu().numpy(), (2, 0, 1))
+    assert got.shape == ref["sens_final"].shape
+    # column-wise relative error: columns differ by many orders of magnitude (d/dpd0 ~ 1e6, d/dalpha ~ 1e2)
+    for c in range(got.shape[2]):
+        assert rel_err(got[:, :, c], ref["sens_final"][:, :, c]) < RTOL64, (name, res.columns[c])
+
+
+@pytest.mark.parametrize("backend", BACKENDS, indirect=True)
+@pytest.mark.parametrize("name", ["ding2003_with_fatigue", "ding2007", "hmed2018_with_fatigue"])
+def test_ivp_fp32_mode(backend, name):
+    pb = random_problem(name, B=16, seed=2)
+    params, x0, win, ctrl = to_lib(pb, backend, dtype=torch.float32)
+    res = fes.ivp(pb["kind"], pb["fat"], params, x0, win, pb["dt"], n_steps=10, ctrl=ctrl, n_shooting=pb["ns"],
+                  dirs=fes.FES_DIR_X0)
+    assert res.x_final.dtype == torch.float32
+    ref = foc.ivp(pb["kind"], pb["fat"], 4, pb["N"], pb["ns"], 10, pb["dt"], pb["tauc"], fo.R0_KM_RELATIONSHIP,
+                  pb["params"], pb["x0"], oracle_win(pb), pb["u"], seed_x0=True)
+    assert rel_err(res.x_final.cpu().numpy().T, ref["final"], floor=1e-3) < RTOL32
+    got = np.transpose(res.sens_final.cpu().numpy(), (2, 0, 1))
+    assert rel_err(got, ref["sens_final"], floor=1e-3) < 20 * RTOL32
+
+
+@pytest.mark.parametrize("backend", BACKENDS, indirect=True)
+def test_ivp_long_fatigue_protocol_matches_oracle(backend):
+    """BASELINE config 2 protocol (33 Hz, 1 s on / 1 s off) for 20 s: 660 intervals x 10 steps, N = 10."""
+    kind, fat = MODELS["ding2003_with_fatigue"]
+    T = 20
+    stim = [s + k / 33 for s in range(0, T, 2) for k in range(33)]
+    ns = 33 * T
+    win, _ = fes.stim_windows(stim, ns, T, 10)
+    B = 8
+    rng = np.random.default_rng(0)
+    params = fes.default_params(kind)[None] * np.concatenate([rng.uniform(0.8, 1.2, (B, 8)), np.ones((B, 6))], axis=1)
+    x0 = np.zeros((B, 5))
+    x0[:, 2], x0[:, 3], x0[:, 4] = params[:, 0], params[:, 2], params[:, 1]
+    res = fes.ivp(kind, fat, torch.tensor(params.T.copy(), device=backend), torch.tensor(x0.T.copy(), device=backend),
+                  torch.tensor(win, device=backend), T / ns, n_steps=10, n_shooting=ns, trace="nodes", dirs=fes.FES_DIR_X0)
+    ref = foc.ivp(kind, fat, 4, 10, ns, 10, T / ns, 0.020, 1.04, params, x0, win[None], None, seed_x0=True, trace_B=B)
+    got = np.transpose(res.trace.cpu().numpy(), (2, 0, 1))
+    assert rel_err(got[:, :, 1], ref["trace"][:, :, 1], floor=1e-6) < RTOL64   # F at every node
+    assert rel_err(res.x_final.cpu().numpy().T, ref["final"]) < RTOL64
+    gs = np.transpose(res.sens_final.cpu().numpy(), (2, 0, 1))
+    # sensitivities w.r.t. Cn0/F0 have decayed to ~1e-300 after 20 s: compare on the scale of the whole block
+    assert np.max(np.abs(gs - ref["sens_final"])) < RTOL64 * np.max(np.abs(ref["sens_final"]))
+
+
+@pytest.mark.parametrize("backend", BACKENDS, indirect=True)
+def test_ivp_argument_errors(backend):
+    from cocofest_b200._lib import FesLibraryError
+
+    pb = random_problem("ding2007", B=4)
+    params, x0, win, ctrl = to_lib(pb, backend)
+    with pytest.raises(ValueError):
+        fes.ivp(pb["kind"], pb["fat"], params, x0, win, pb["dt"], ctrl=None, n_shooting=pb["ns"])
+    with pytest.raises(ValueError):
+        fes.ivp(pb["kind"], pb["fat"], params, x0, win, pb["dt"], ctrl=ctrl, n_shooting=pb["ns"], dirs=fes.FES_DIR_U)
+    with pytest.raises(FesLibraryError):
+        fes.ivp(pb["kind"], pb["fat"], params, x0, win, pb["dt"], ctrl=ctrl, n_shooting=pb["ns"], scheme=3)
+    with pytest.raises(FesLibraryError):
+        fes.ivp(pb["kind"], pb["fat"], params, x0, win, pb["dt"], ctrl=ctrl, n_shooting=pb["ns"], n_steps=1000)
