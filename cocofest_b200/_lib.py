@@ -8,8 +8,11 @@ import ctypes
 from ctypes import POINTER, Structure, c_char_p, c_double, c_int, c_int32, c_int64, c_void_p
 from pathlib import Path
 
+import os
+
 CSRC = Path(__file__).resolve().parent / "csrc"
-LIB_PATH = CSRC / "libfes_b200.so"
+# FES_B200_LIB points at another build of the SAME library (launch-shape sweeps, scripts/build_variants.sh)
+LIB_PATH = Path(os.environ["FES_B200_LIB"]) if os.environ.get("FES_B200_LIB") else CSRC / "libfes_b200.so"
 
 FES_ABI_VERSION = 1
 FES_DING2003, FES_DING2007, FES_HMED2018 = 0, 1, 2

@@ -89,6 +89,22 @@ constexpr bool dir_has_cn(int c) {
     return c == D_CN0 || c == D_INT || c == D_WT || c == D_KM_REST || c == D_AR || c == D_BS || c == D_IS || c == D_CR;
 }
 constexpr bool dir_has_dg(int c) { return c == D_PW || c == D_PD0 || c == D_PDT; }
+// Fatigue models: the rows A', Tau1', Km' are linear with the SAME decay 1/tau_fat and are all driven by F
+// alone, so for every direction that does not force those rows (initial states, controls, pulse times) the
+// tangent (vA, vTau1, vKm) stays in a 1-dimensional affine family:
+//     vA = alpha_a W + mA,  vTau1 = alpha_tau1 W + mT1,  vKm = alpha_km W + mKm,
+//     W' = vF - W/tau_fat  (W = 0 at the seed),   m' = -m/tau_fat  (m = the seeded component).
+// Runge-Kutta maps commute with constant linear embeddings, so pushing (vCn, vF, W) and ONE shared decaying
+// scalar through the stages gives the tangent of the discrete map exactly (not an approximation of it);
+// such a "reduced" column carries 2 or 3 numbers instead of 5.  The Cn0 column's own Cn component is the
+// second shared scalar (vCn' = -vCn/tauc), which leaves that column with (vF, W) as well.
+constexpr bool dir_reduced(bool fat, int c) { return fat && c <= D_WT; }
+// components stored in V[d][...] for a column of code c: [first, last)
+constexpr int dir_first(bool fat, int c) {
+    if (dir_reduced(fat, c)) return (dir_has_cn(c) && c != D_CN0) ? 0 : 1;
+    return dir_has_cn(c) ? 0 : 1;
+}
+constexpr int dir_last(bool fat, int c) { return dir_reduced(fat, c) ? 3 : (fat ? 5 : 2); }
 
 template <int I, int N, class F>
 FES_HD void static_for(F &&f) {
@@ -255,6 +271,7 @@ FES_HD void interval_setup(const Traj<T> &tr, TF tab, CF ctl, int N, int tile_of
 template <typename T>
 struct Stage {  // the non-trivial entries of d f / d (x, params) at a stage point
     T cF, cCn, cKm, cT1, cA, cT2, cG, Fs, dA, dT1, dKm;
+    T cW;  // fatigue: d F' / d W = cA alpha_a + cT1 alpha_tau1 + cKm alpha_km  (reduced columns)
 };
 
 template <typename T, int KIND, bool FAT, bool NEED>
@@ -282,14 +299,15 @@ FES_HD void nominal_rhs(const Traj<T> &tr, T Ee, T g, const T *x, T *k, Stage<T>
         const T ct1 = f * invD * invD;       // d F' / d tau1
         st.cT1 = ct1;
         const T Gc = xfma(ct1, tr.tau2, Aeff);  // d F' / d q
-        const T is2 = is * is;
-        st.cCn = Gc * (km * is2);
-        st.cKm = -(Gc * (cn * is2));
+        const T u = Gc * is;                    // d q / d Cn = (1 - q)/(Km + Cn),  d q / d Km = -q/(Km + Cn)
+        st.cKm = -(u * q);
+        st.cCn = u + st.cKm;
         st.cA = (KIND == DING2007) ? q * g : q;
         st.cT2 = ct1 * q;
         st.cG = A * q;
         st.Fs = f;
         if constexpr (FAT) {
+            st.cW = xfma(st.cA, tr.alpha_a, xfma(st.cT1, tr.alpha_tau1, st.cKm * tr.alpha_km));
             st.dA = (A - tr.a_rest) * tr.kappa2;   // d/d tau_fat of -(A - A_rest)/tau_fat
             st.dT1 = (t1 - tr.tau1_rest) * tr.kappa2;
             st.dKm = (km - tr.km_rest) * tr.kappa2;
@@ -342,104 +360,183 @@ FES_HD void column_rhs(const Traj<T> &tr, const Stage<T> &st, T eps, T sE, T dg,
     }
 }
 
-// ---- one RK step (scheme = 1, 2 or 4) of the state and of every tangent column -----------
-// e0, e1, e2 = eps at the step start, midpoint and end (relative to the interval start).
+// ---- one RK stage of one REDUCED tangent column (fatigue models, see dir_reduced) ------------
+// v = (vCn, vF, W); mu / nu = the shared decaying scalars (fatigue mode, Cn mode) at this stage point.
+template <typename T, int KIND, int CODE>
+FES_HD void column_rhs_red(const Traj<T> &tr, const Stage<T> &st, T eps, T sE, T dg, T mu, T nu, const T *v, T *k) {
+    T kf = xfma(st.cW, v[2], st.cF * v[1]);
+    if constexpr (CODE == D_CN0) {
+        kf = xfma(st.cCn, nu, kf);
+    } else if constexpr (dir_has_cn(CODE)) {
+        k[0] = xfma(sE, eps, -v[0]) * tr.inv_tauc;
+        kf = xfma(st.cCn, v[0], kf);
+    }
+    if constexpr (CODE == D_A0) kf = xfma(st.cA, mu, kf);
+    if constexpr (CODE == D_TAU10) kf = xfma(st.cT1, mu, kf);
+    if constexpr (CODE == D_KM0) kf = xfma(st.cKm, mu, kf);
+    if constexpr (dir_has_dg(CODE)) kf = xfma(st.cG, dg, kf);
+    k[1] = kf;
+    k[2] = xfma(-tr.kappa, v[2], v[1]);
+}
+
+// ---- tangent state of one trajectory ----------------------------------------------------------
+// V[d] holds the stored components of column d (dir_first .. dir_last); mu, nu are the two shared decaying
+// scalars of the reduced columns.  They are kept in double in the f32 build too: a float cannot represent
+// 1 - h/tau_fat (h/tau_fat ~ 2e-5) to better than 0.3 % of the decay rate, and the fp64 pipe is idle there.
 template <typename T, int KIND, bool FAT, int GROUPS>
-FES_HD void rk_step(const Traj<T> &tr, const Interval<T, Dirs<KIND, FAT, GROUPS>::ND> &iv, int scheme, T h,
-                    T e0, T e1, T e2, T *x, T (*V)[FAT ? 5 : 2]) {
+struct Tangent {
     using D = Dirs<KIND, FAT, GROUPS>;
-    constexpr int NX = D::NX;
-    constexpr int ND = D::ND;
-    constexpr bool NEED = ND > 0;
-    const T hh = h * T(0.5), h6 = h * T(1.0 / 6.0), h3 = h * T(1.0 / 3.0);
-    Stage<T> st[4];
-    {
-        T k[NX], xs[NX], xn[NX];
-        nominal_rhs<T, KIND, FAT, NEED>(tr, iv.E * e0, iv.g, x, k, st[0]);
-        if (scheme == 1) {
+    T V[D::ND > 0 ? D::ND : 1][D::NX];
+    double mu, nu;
+
+    FES_HD void init() {
+        static_for<0, D::ND>([&](auto ic) {
+            constexpr int d = decltype(ic)::value;
+            constexpr int C = D::code(d);
 #pragma unroll
-            for (int j = 0; j < NX; ++j) x[j] = xfma(h, k[j], x[j]);
+            for (int j = 0; j < D::NX; ++j) {
+                if constexpr (dir_reduced(FAT, C)) V[d][j] = (C == D_F0 && j == 1) ? T(1) : T(0);
+                else V[d][j] = (d < D::n_x0 && j == d) ? T(1) : T(0);
+            }
+        });
+        mu = 1.0;
+        nu = 1.0;
+    }
+    // component j of the actual tangent column d (what the caller sees)
+    template <int d>
+    FES_HD T get(const Traj<T> &tr, int j) const {
+        constexpr int C = D::code(d);
+        if constexpr (!dir_reduced(FAT, C)) {
+            return V[d][j];
         } else {
-#pragma unroll
-            for (int j = 0; j < NX; ++j) {
-                xs[j] = xfma(hh, k[j], x[j]);
-                xn[j] = xfma(h6, k[j], x[j]);
-            }
-            const T Ee1 = iv.E * e1;
-            nominal_rhs<T, KIND, FAT, NEED>(tr, Ee1, iv.g, xs, k, st[1]);
-            if (scheme == 2) {
-#pragma unroll
-                for (int j = 0; j < NX; ++j) x[j] = xfma(h, k[j], x[j]);
-            } else {
-#pragma unroll
-                for (int j = 0; j < NX; ++j) {
-                    xs[j] = xfma(hh, k[j], x[j]);
-                    xn[j] = xfma(h3, k[j], xn[j]);
-                }
-                nominal_rhs<T, KIND, FAT, NEED>(tr, Ee1, iv.g, xs, k, st[2]);
-#pragma unroll
-                for (int j = 0; j < NX; ++j) {
-                    xs[j] = xfma(h, k[j], x[j]);
-                    xn[j] = xfma(h3, k[j], xn[j]);
-                }
-                nominal_rhs<T, KIND, FAT, NEED>(tr, iv.E * e2, iv.g, xs, k, st[3]);
-#pragma unroll
-                for (int j = 0; j < NX; ++j) x[j] = xfma(h6, k[j], xn[j]);
-            }
+            if (j == 0) return C == D_CN0 ? (T)nu : (dir_has_cn(C) ? V[d][0] : T(0));
+            if (j == 1) return V[d][1];
+            const T m = (T)mu;
+            if (j == 2) return xfma(tr.alpha_a, V[d][2], C == D_A0 ? m : T(0));
+            if (j == 3) return xfma(tr.alpha_tau1, V[d][2], C == D_TAU10 ? m : T(0));
+            return xfma(tr.alpha_km, V[d][2], C == D_KM0 ? m : T(0));
         }
     }
+};
+
+// ---- one RK step of the state and of every tangent column ------------------------------------
+// Butcher data of the three explicit schemes bioptim offers (integrator.py:324-365), in units of h:
+//   stage s is evaluated at x + alpha_s h k_{s-1};  the step adds beta_s h k_s.
+template <int SCHEME> struct Tableau;
+template <> struct Tableau<1> {
+    static constexpr int NS = 1;
+    static constexpr double alpha(int) { return 0.0; }
+    static constexpr double beta(int) { return 1.0; }
+    static constexpr int eps_at(int) { return 0; }
+};
+template <> struct Tableau<2> {  // midpoint
+    static constexpr int NS = 2;
+    static constexpr double alpha(int s) { return s == 1 ? 0.5 : 0.0; }
+    static constexpr double beta(int s) { return s == 1 ? 1.0 : 0.0; }
+    static constexpr int eps_at(int s) { return s; }
+};
+template <> struct Tableau<4> {
+    static constexpr int NS = 4;
+    static constexpr double alpha(int s) { return s == 0 ? 0.0 : (s == 3 ? 1.0 : 0.5); }
+    static constexpr double beta(int s) { return (s == 0 || s == 3) ? 1.0 / 6.0 : 1.0 / 3.0; }
+    static constexpr int eps_at(int s) { return s == 0 ? 0 : (s == 3 ? 2 : 1); }
+};
+
+// Straight-line code, stage-major: the nominal stage s produces the Jacobian entries that every column's
+// stage s consumes, so only ONE Stage record is live at a time and the columns (independent of each other)
+// sit in one basic block where the compiler interleaves their FMA chains.
+// e[0], e[1], e[2] = eps at the step start, midpoint and end (relative to the interval start).
+template <typename T, int KIND, bool FAT, int GROUPS, int SCHEME>
+FES_HD void rk_step_scheme(const Traj<T> &tr, const Interval<T, Dirs<KIND, FAT, GROUPS>::ND> &iv, T h, const T *e,
+                           T *x, Tangent<T, KIND, FAT, GROUPS> &tg) {
+    using D = Dirs<KIND, FAT, GROUPS>;
+    using TB = Tableau<SCHEME>;
+    constexpr int NX = D::NX;
+    constexpr int ND = D::ND;
+    constexpr int NS = TB::NS;
+    constexpr bool NEED = ND > 0;
+    constexpr bool MODES = FAT && (D::n_x0 > 0);
+    T xs[NX], xn[NX];
+#pragma unroll
+    for (int j = 0; j < NX; ++j) xs[j] = xn[j] = x[j];
+    T vs[ND > 0 ? ND : 1][NX], vn[ND > 0 ? ND : 1][NX];
+    static_for<0, ND>([&](auto ic) {
+        constexpr int d = decltype(ic)::value;
+#pragma unroll
+        for (int j = 0; j < NX; ++j) vs[d][j] = vn[d][j] = tg.V[d][j];
+    });
+    // the two shared decaying scalars of the reduced columns obey m' = -(z / h) m: same scheme, in double
+    const double zf = (double)tr.kappa * (double)h, zc = (double)tr.inv_tauc * (double)h;
+    double mus = tg.mu, mun = tg.mu, nus = tg.nu, nun = tg.nu;
+
+    static_for<0, NS>([&](auto is) {
+        constexpr int s = decltype(is)::value;
+        constexpr bool LAST = s == NS - 1;
+        const T hb = h * T(TB::beta(s));
+        const T ha = h * T(LAST ? 0.0 : TB::alpha(s + 1));
+        const T eps = e[TB::eps_at(s)];
+        Stage<T> st;
+        {
+            T k[NX];
+            nominal_rhs<T, KIND, FAT, NEED>(tr, iv.E * eps, iv.g, xs, k, st);
+#pragma unroll
+            for (int j = 0; j < NX; ++j) {
+                if constexpr (TB::beta(s) != 0.0) xn[j] = xfma(hb, k[j], xn[j]);
+                if constexpr (!LAST) xs[j] = xfma(ha, k[j], x[j]);
+            }
+        }
+        T mu_s = T(0), nu_s = T(0);
+        if constexpr (MODES) {
+            mu_s = (T)mus;
+            nu_s = (T)nus;
+            if constexpr (TB::beta(s) != 0.0) {
+                mun = fma(-zf * TB::beta(s), mus, mun);
+                nun = fma(-zc * TB::beta(s), nus, nun);
+            }
+            if constexpr (!LAST) {
+                mus = fma(-zf * TB::alpha(s + 1), mus, tg.mu);
+                nus = fma(-zc * TB::alpha(s + 1), nus, tg.nu);
+            }
+        }
+        static_for<0, ND>([&](auto ic) {
+            constexpr int d = decltype(ic)::value;
+            constexpr int C = D::code(d);
+            // stored components of this column: Cn only for the directions that reach it; (vF, W) when reduced
+            constexpr int J0 = dir_first(FAT, C), J1 = dir_last(FAT, C);
+            T k[NX];
+            if constexpr (dir_reduced(FAT, C))
+                column_rhs_red<T, KIND, C>(tr, st, eps, iv.sE[d], iv.dg[d], mu_s, nu_s, vs[d], k);
+            else
+                column_rhs<T, KIND, FAT, C>(tr, st, eps, iv.sE[d], iv.dg[d], vs[d], k);
+#pragma unroll
+            for (int j = J0; j < J1; ++j) {
+                if constexpr (TB::beta(s) != 0.0) vn[d][j] = xfma(hb, k[j], vn[d][j]);
+                if constexpr (!LAST) vs[d][j] = xfma(ha, k[j], tg.V[d][j]);
+            }
+        });
+    });
+#pragma unroll
+    for (int j = 0; j < NX; ++j) x[j] = xn[j];
     static_for<0, ND>([&](auto ic) {
         constexpr int d = decltype(ic)::value;
         constexpr int C = D::code(d);
-        // components of this column that can be non-zero: Cn only for the directions that reach it
-        constexpr int J0 = dir_has_cn(C) ? 0 : 1;
-        T *v = V[d];
-        const T sE = iv.sE[d], dg = iv.dg[d];
-        T k[NX], vs[NX], vn[NX];
-        column_rhs<T, KIND, FAT, C>(tr, st[0], e0, sE, dg, v, k);
-        if (scheme == 1) {
 #pragma unroll
-            for (int j = J0; j < NX; ++j) v[j] = xfma(h, k[j], v[j]);
-        } else {
-            vs[0] = T(0);
-#pragma unroll
-            for (int j = J0; j < NX; ++j) {
-                vs[j] = xfma(hh, k[j], v[j]);
-                vn[j] = xfma(h6, k[j], v[j]);
-            }
-            column_rhs<T, KIND, FAT, C>(tr, st[1], e1, sE, dg, vs, k);
-            if (scheme == 2) {
-#pragma unroll
-                for (int j = J0; j < NX; ++j) v[j] = xfma(h, k[j], v[j]);
-            } else {
-#pragma unroll
-                for (int j = J0; j < NX; ++j) {
-                    vs[j] = xfma(hh, k[j], v[j]);
-                    vn[j] = xfma(h3, k[j], vn[j]);
-                }
-                column_rhs<T, KIND, FAT, C>(tr, st[2], e1, sE, dg, vs, k);
-#pragma unroll
-                for (int j = J0; j < NX; ++j) {
-                    vs[j] = xfma(h, k[j], v[j]);
-                    vn[j] = xfma(h3, k[j], vn[j]);
-                }
-                column_rhs<T, KIND, FAT, C>(tr, st[3], e2, sE, dg, vs, k);
-#pragma unroll
-                for (int j = J0; j < NX; ++j) v[j] = xfma(h6, k[j], vn[j]);
-            }
-        }
+        for (int j = dir_first(FAT, C); j < dir_last(FAT, C); ++j) tg.V[d][j] = vn[d][j];
     });
+    if constexpr (MODES) {
+        tg.mu = mun;
+        tg.nu = nun;
+    }
 }
 
-// initial value of the tangent columns at the start of an interval (shoot) or of the IVP
+// e0, e1, e2 = eps at the step start, midpoint and end.  ONE uniform branch per step selects the scheme.
 template <typename T, int KIND, bool FAT, int GROUPS>
-FES_HD void init_columns(T (*V)[FAT ? 5 : 2]) {
-    using D = Dirs<KIND, FAT, GROUPS>;
-    static_for<0, D::ND>([&](auto ic) {
-        constexpr int d = decltype(ic)::value;
-#pragma unroll
-        for (int j = 0; j < D::NX; ++j) V[d][j] = (d < D::n_x0 && j == d) ? T(1) : T(0);
-    });
+FES_HD void rk_step(const Traj<T> &tr, const Interval<T, Dirs<KIND, FAT, GROUPS>::ND> &iv, int scheme, T h,
+                    T e0, T e1, T e2, T *x, Tangent<T, KIND, FAT, GROUPS> &tg) {
+    const T e[3] = {e0, e1, e2};
+    if (scheme == 4) rk_step_scheme<T, KIND, FAT, GROUPS, 4>(tr, iv, h, e, x, tg);
+    else if (scheme == 2) rk_step_scheme<T, KIND, FAT, GROUPS, 2>(tr, iv, h, e, x, tg);
+    else rk_step_scheme<T, KIND, FAT, GROUPS, 1>(tr, iv, h, e, x, tg);
 }
 
 }  // namespace fes

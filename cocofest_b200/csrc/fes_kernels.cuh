@@ -21,7 +21,24 @@
 
 namespace fes {
 
-constexpr int BLOCK = 128;
+// launch shape: tuned on a B200 (scripts/tune_ivp.py, profiles/r01_tune_ivp.txt); overridable for that sweep only
+#ifndef FES_BLOCK
+#define FES_BLOCK 128
+#endif
+constexpr int BLOCK = FES_BLOCK;
+// Resident blocks per SM the compiler must make room for.  The fp64 fatigue kernels whose columns are all
+// "reduced" (fes_core.cuh) need ~185-200 registers unconstrained = 2 blocks/SM; capping them at 168 registers
+// (3 blocks = 12 warps/SM) costs ~60 bytes of spill and measured +7 % on a B200 (profiles/r01_tune_ivp.txt).
+template <typename T, int KIND, bool FAT, int GROUPS>
+constexpr int min_blocks() {
+#ifdef FES_MIN_BLOCKS
+    return FES_MIN_BLOCKS;
+#else
+    constexpr bool red = FAT && (GROUPS == G_X0 || GROUPS == G_U || GROUPS == G_W || (GROUPS == (G_X0 | G_U) && KIND == DING2007));
+    return (sizeof(T) == 8 && red) ? 3 : 2;
+#endif
+}
+#define FES_LAUNCH_BOUNDS __launch_bounds__(BLOCK, (min_blocks<T, KIND, FAT, GROUPS>()))
 
 template <typename T>
 struct IvpArgs {
@@ -82,7 +99,7 @@ __global__ void fes_tables_kernel(const double *__restrict__ win, int64_t wB, in
 
 // ---------------------------------------------------------------------------------------------
 template <typename T, int KIND, bool FAT, int GROUPS>
-__global__ void __launch_bounds__(BLOCK) fes_ivp_kernel(const IvpArgs<T> a) {
+__global__ void FES_LAUNCH_BOUNDS fes_ivp_kernel(const IvpArgs<T> a) {
     using D = Dirs<KIND, FAT, GROUPS>;
     constexpr int NX = D::NX;
     constexpr int ND = D::ND;
@@ -102,8 +119,8 @@ __global__ void __launch_bounds__(BLOCK) fes_ivp_kernel(const IvpArgs<T> a) {
     T x[NX];
 #pragma unroll
     for (int j = 0; j < NX; ++j) x[j] = a.x0[j * a.B + bb];
-    T V[ND > 0 ? ND : 1][NX];
-    init_columns<T, KIND, FAT, GROUPS>(V);
+    Tangent<T, KIND, FAT, GROUPS> tg;
+    tg.init();
 
     const bool tr_on = live && a.trace_mode != 0 && b < a.trace_B;
     auto put_state = [&](int64_t pt) {
@@ -118,7 +135,7 @@ __global__ void __launch_bounds__(BLOCK) fes_ivp_kernel(const IvpArgs<T> a) {
                 static_for<0, ND>([&](auto ic) {
                     constexpr int d = decltype(ic)::value;
 #pragma unroll
-                    for (int j = 0; j < NX; ++j) a.sens_trace[((node * NX + j) * ND + d) * a.trace_B + b] = V[d][j];
+                    for (int j = 0; j < NX; ++j) a.sens_trace[((node * NX + j) * ND + d) * a.trace_B + b] = tg.template get<d>(tr, j);
                 });
             }
         }
@@ -154,7 +171,7 @@ __global__ void __launch_bounds__(BLOCK) fes_ivp_kernel(const IvpArgs<T> a) {
             interval_setup<T, KIND, FAT, GROUPS>(
                 tr, [&](int c) { return trow[c * tstr]; }, [&](int c) { return crow[c * cstr]; }, a.N, a.tile_off, iv);
             for (int i = 0; i < a.S; ++i) {
-                rk_step<T, KIND, FAT, GROUPS>(tr, iv, a.scheme, a.h, s_eps[2 * i], s_eps[2 * i + 1], s_eps[2 * i + 2], x, V);
+                rk_step<T, KIND, FAT, GROUPS>(tr, iv, a.scheme, a.h, s_eps[2 * i], s_eps[2 * i + 1], s_eps[2 * i + 2], x, tg);
                 if (tr_on && a.trace_mode == 1) put_state((int64_t)node * a.S + i + 1);
             }
             if (tr_on) {
@@ -171,7 +188,7 @@ __global__ void __launch_bounds__(BLOCK) fes_ivp_kernel(const IvpArgs<T> a) {
                 static_for<0, ND>([&](auto ic) {
                     constexpr int d = decltype(ic)::value;
 #pragma unroll
-                    for (int j = 0; j < NX; ++j) a.sens_final[(j * ND + d) * a.B + b] = V[d][j];
+                    for (int j = 0; j < NX; ++j) a.sens_final[(j * ND + d) * a.B + b] = tg.template get<d>(tr, j);
                 });
             }
         }
@@ -180,7 +197,7 @@ __global__ void __launch_bounds__(BLOCK) fes_ivp_kernel(const IvpArgs<T> a) {
 
 // ---------------------------------------------------------------------------------------------
 template <typename T, int KIND, bool FAT, int GROUPS>
-__global__ void __launch_bounds__(BLOCK) fes_shoot_kernel(const ShootArgs<T> a) {
+__global__ void FES_LAUNCH_BOUNDS fes_shoot_kernel(const ShootArgs<T> a) {
     using D = Dirs<KIND, FAT, GROUPS>;
     constexpr int NX = D::NX;
     constexpr int ND = D::ND;
@@ -198,8 +215,8 @@ __global__ void __launch_bounds__(BLOCK) fes_shoot_kernel(const ShootArgs<T> a) 
     T x[NX];
 #pragma unroll
     for (int j = 0; j < NX; ++j) x[j] = __ldg(a.X + (k * NX + j) * a.B + b);
-    T V[ND > 0 ? ND : 1][NX];
-    init_columns<T, KIND, FAT, GROUPS>(V);
+    Tangent<T, KIND, FAT, GROUPS> tg;
+    tg.init();
 
     const T *trow = a.tab + k * a.row * a.tB + b * a.tS;
     const T *crow = a.ctrl + k * a.nu * a.cB + b * a.cS;
@@ -208,7 +225,7 @@ __global__ void __launch_bounds__(BLOCK) fes_shoot_kernel(const ShootArgs<T> a) 
         tr, [&](int c) { return __ldg(trow + c * a.tB); }, [&](int c) { return __ldg(crow + c * a.cB); }, a.N,
         a.tile_off, iv);
     for (int i = 0; i < a.S; ++i)
-        rk_step<T, KIND, FAT, GROUPS>(tr, iv, a.scheme, a.h, s_eps[2 * i], s_eps[2 * i + 1], s_eps[2 * i + 2], x, V);
+        rk_step<T, KIND, FAT, GROUPS>(tr, iv, a.scheme, a.h, s_eps[2 * i], s_eps[2 * i + 1], s_eps[2 * i + 2], x, tg);
 
 #pragma unroll
     for (int j = 0; j < NX; ++j) {
@@ -220,7 +237,7 @@ __global__ void __launch_bounds__(BLOCK) fes_shoot_kernel(const ShootArgs<T> a) 
             static_for<0, ND>([&](auto ic) {
                 constexpr int d = decltype(ic)::value;
 #pragma unroll
-                for (int j = 0; j < NX; ++j) a.J[((k * NX + j) * a.j_cols + a.j_col0 + d) * a.B + b] = V[d][j];
+                for (int j = 0; j < NX; ++j) a.J[((k * NX + j) * a.j_cols + a.j_col0 + d) * a.B + b] = tg.template get<d>(tr, j);
             });
         }
     }

@@ -56,16 +56,19 @@ int ivp_cpu(const IvpArgs<T> &a) {
         load_traj(tr, [&](int j) { return a.params[j * a.pB + b * a.pS]; }, a.tauc, a.r0_km);
         T x[NX];
         for (int j = 0; j < NX; ++j) x[j] = a.x0[j * a.B + b];
-        T V[ND > 0 ? ND : 1][NX];
-        init_columns<T, KIND, FAT, GROUPS>(V);
+        Tangent<T, KIND, FAT, GROUPS> tg;
+        tg.init();
         const bool tr_on = a.trace_mode != 0 && b < a.trace_B;
         auto put_state = [&](int64_t pt) {
             if (a.trace) for (int j = 0; j < NX; ++j) a.trace[(pt * NX + j) * a.trace_B + b] = x[j];
         };
         auto put_sens = [&](int64_t node) {
             if (ND > 0 && a.sens_trace)
-                for (int d = 0; d < ND; ++d)
-                    for (int j = 0; j < NX; ++j) a.sens_trace[((node * NX + j) * ND + d) * a.trace_B + b] = V[d][j];
+                static_for<0, ND>([&](auto ic) {
+                    constexpr int d = decltype(ic)::value;
+                    for (int j = 0; j < NX; ++j)
+                        a.sens_trace[((node * NX + j) * ND + d) * a.trace_B + b] = tg.template get<d>(tr, j);
+                });
         };
         if (tr_on) { put_state(0); put_sens(0); }
         for (int node = 0; node < a.ns; ++node) {
@@ -75,7 +78,7 @@ int ivp_cpu(const IvpArgs<T> &a) {
             interval_setup<T, KIND, FAT, GROUPS>(
                 tr, [&](int c) { return trow[c * a.tB]; }, [&](int c) { return crow[c * a.cB]; }, a.N, a.tile_off, iv);
             for (int i = 0; i < a.S; ++i) {
-                rk_step<T, KIND, FAT, GROUPS>(tr, iv, a.scheme, a.h, a.eps[2 * i], a.eps[2 * i + 1], a.eps[2 * i + 2], x, V);
+                rk_step<T, KIND, FAT, GROUPS>(tr, iv, a.scheme, a.h, a.eps[2 * i], a.eps[2 * i + 1], a.eps[2 * i + 2], x, tg);
                 if (tr_on && a.trace_mode == 1) put_state((int64_t)node * a.S + i + 1);
             }
             if (tr_on) {
@@ -85,8 +88,10 @@ int ivp_cpu(const IvpArgs<T> &a) {
         }
         for (int j = 0; j < NX; ++j) a.x_final[j * a.B + b] = x[j];
         if (ND > 0 && a.sens_final)
-            for (int d = 0; d < ND; ++d)
-                for (int j = 0; j < NX; ++j) a.sens_final[(j * ND + d) * a.B + b] = V[d][j];
+            static_for<0, ND>([&](auto ic) {
+                constexpr int d = decltype(ic)::value;
+                for (int j = 0; j < NX; ++j) a.sens_final[(j * ND + d) * a.B + b] = tg.template get<d>(tr, j);
+            });
     }
     return 0;
 }
@@ -101,22 +106,25 @@ int shoot_cpu(const ShootArgs<T> &a) {
             load_traj(tr, [&](int j) { return a.params[j * a.pB + b * a.pS]; }, a.tauc, a.r0_km);
             T x[NX];
             for (int j = 0; j < NX; ++j) x[j] = a.X[(k * NX + j) * a.B + b];
-            T V[ND > 0 ? ND : 1][NX];
-            init_columns<T, KIND, FAT, GROUPS>(V);
+            Tangent<T, KIND, FAT, GROUPS> tg;
+            tg.init();
             const T *trow = a.tab + k * a.row * a.tB + b * a.tS;
             const T *crow = a.ctrl + k * a.nu * a.cB + b * a.cS;
             Interval<T, ND> iv;
             interval_setup<T, KIND, FAT, GROUPS>(
                 tr, [&](int c) { return trow[c * a.tB]; }, [&](int c) { return crow[c * a.cB]; }, a.N, a.tile_off, iv);
             for (int i = 0; i < a.S; ++i)
-                rk_step<T, KIND, FAT, GROUPS>(tr, iv, a.scheme, a.h, a.eps[2 * i], a.eps[2 * i + 1], a.eps[2 * i + 2], x, V);
+                rk_step<T, KIND, FAT, GROUPS>(tr, iv, a.scheme, a.h, a.eps[2 * i], a.eps[2 * i + 1], a.eps[2 * i + 2], x, tg);
             for (int j = 0; j < NX; ++j) {
                 if (a.Phi) a.Phi[(k * NX + j) * a.B + b] = x[j];
                 if (a.G) a.G[(k * NX + j) * a.B + b] = a.X[((k + 1) * NX + j) * a.B + b] - x[j];
             }
             if (ND > 0 && a.J)
-                for (int d = 0; d < ND; ++d)
-                    for (int j = 0; j < NX; ++j) a.J[((k * NX + j) * a.j_cols + a.j_col0 + d) * a.B + b] = V[d][j];
+                static_for<0, ND>([&](auto ic) {
+                    constexpr int d = decltype(ic)::value;
+                    for (int j = 0; j < NX; ++j)
+                        a.J[((k * NX + j) * a.j_cols + a.j_col0 + d) * a.B + b] = tg.template get<d>(tr, j);
+                });
         }
     return 0;
 }
