@@ -19,7 +19,7 @@ FES_DING2003, FES_DING2007, FES_HMED2018 = 0, 1, 2
 FES_NP = 14
 FES_DIR_X0, FES_DIR_U, FES_DIR_P, FES_DIR_W, FES_DIR_PF = 1, 2, 4, 8, 16
 FES_TILE = 5
-FES_PARAMS_SHARED, FES_WIN_SHARED, FES_CTRL_SHARED, FES_TABLES_READY = 1, 2, 4, 8
+FES_PARAMS_SHARED, FES_WIN_SHARED, FES_CTRL_SHARED, FES_TABLES_READY, FES_TARGET_SHARED = 1, 2, 4, 8, 16
 
 PARAM_NAMES = ("a_rest", "km_rest", "tau1_rest", "tau2", "alpha_a", "alpha_tau1", "alpha_km", "tau_fat",
                "pd0", "pdt", "ar", "bs", "Is", "cr")
@@ -57,6 +57,18 @@ class FesShootBuffers(Structure):
     ]
 
 
+class FesIdentBuffers(Structure):
+    _fields_ = [
+        ("params", c_void_p), ("x0", c_void_p), ("stim_win", c_void_p), ("ctrl", c_void_p), ("target", c_void_p),
+        ("weight", c_void_p), ("lower", c_void_p), ("upper", c_void_p), ("params_out", c_void_p), ("cost", c_void_p),
+        ("grad", c_void_p), ("hess", c_void_p), ("iters", c_void_p), ("workspace", c_void_p), ("workspace_bytes", c_int64),
+    ]
+
+
+class FesIdentOptions(Structure):
+    _fields_ = [("max_iter", c_int32), ("p_mask", c_int32), ("lambda0", c_double), ("ftol", c_double), ("xtol", c_double)]
+
+
 # every symbol include/fes_b200.h declares, with its prototype
 PROTOTYPES = {
     "fes_version": (c_int, []),
@@ -73,6 +85,10 @@ PROTOTYPES = {
     "fes_ivp_host_f32": (c_int, [POINTER(FesDesc), POINTER(FesIvpBuffers), c_void_p]),
     "fes_shoot_host_f64": (c_int, [POINTER(FesDesc), POINTER(FesShootBuffers), c_void_p]),
     "fes_shoot_host_f32": (c_int, [POINTER(FesDesc), POINTER(FesShootBuffers), c_void_p]),
+    "fes_identify_f64": (c_int, [POINTER(FesDesc), POINTER(FesIdentBuffers), POINTER(FesIdentOptions), c_void_p]),
+    "fes_identify_f32": (c_int, [POINTER(FesDesc), POINTER(FesIdentBuffers), POINTER(FesIdentOptions), c_void_p]),
+    "fes_identify_host_f64": (c_int, [POINTER(FesDesc), POINTER(FesIdentBuffers), POINTER(FesIdentOptions), c_void_p]),
+    "fes_identify_host_f32": (c_int, [POINTER(FesDesc), POINTER(FesIdentBuffers), POINTER(FesIdentOptions), c_void_p]),
     "fes_probe_fma_peak": (c_int, [c_int, c_int, c_void_p, POINTER(c_double)]),
     "fes_launch_count": (c_int64, []),
 }

@@ -8,6 +8,7 @@
 
 #include "fes_b200.h"
 #include "fes_kernels.cuh"
+#include "fes_ident.cuh"
 
 namespace fes {
 namespace abi {
@@ -136,6 +137,65 @@ void fill_shoot_args(const FesDesc *d, const FesShootBuffers *b, const Carve &c,
     a.h = (T)(d->dt / d->n_steps);
     a.tauc = (T)d->tauc;
     a.r0_km = (T)d->r0_km;
+}
+
+inline int ident_num_params(int kind) { return kind == FES_DING2003 ? 4 : (kind == FES_DING2007 ? 6 : 8); }
+
+inline int check_ident(const FesDesc *d, const FesIdentBuffers *b, const FesIdentOptions *o) {
+    int rc = check_desc(d, true);
+    if (rc) return rc;
+    if (d->fatigue != 0) return E_MODEL;   // ding2003_force_parameter_identification.py:196-199
+    if (d->dirs != FES_DIR_P) return E_DIRS;
+    if (b == nullptr || o == nullptr || b->params == nullptr || b->target == nullptr || b->params_out == nullptr ||
+        b->cost == nullptr || b->grad == nullptr || b->hess == nullptr)
+        return E_BUF;
+    if (num_controls(d->model_kind, d->n_trunc) > 0 && b->ctrl == nullptr) return E_BUF;
+    if (o->max_iter < 0 || o->max_iter > 10000 || !(o->lambda0 > 0.0) || !(o->ftol >= 0.0) || !(o->xtol >= 0.0)) return E_SIZE;
+    if (o->p_mask < 0 || o->p_mask >= (1 << ident_num_params(d->model_kind))) return E_DIRS;
+    return E_OK;
+}
+
+template <typename T>
+void fill_ident_args(const FesDesc *d, const FesIdentBuffers *b, const FesIdentOptions *o, const Carve &c, IdentArgs<T> &a) {
+    std::memset(&a, 0, sizeof(a));
+    a.params = (const T *)b->params;
+    a.pB = (d->flags & FES_PARAMS_SHARED) ? 1 : d->batch;
+    a.pS = (d->flags & FES_PARAMS_SHARED) ? 0 : 1;
+    a.x0 = (const T *)b->x0;
+    a.tab = reinterpret_cast<const T *>((char *)b->workspace + c.tab_off);
+    a.tB = c.tB;
+    a.tS = (d->flags & FES_WIN_SHARED) ? 0 : 1;
+    a.row = c.row;
+    a.eps = reinterpret_cast<const T *>((char *)b->workspace + c.eps_off);
+    a.ctrl = (const T *)b->ctrl;
+    a.cB = (d->flags & FES_CTRL_SHARED) ? 1 : d->batch;
+    a.cS = (d->flags & FES_CTRL_SHARED) ? 0 : 1;
+    a.nu = num_controls(d->model_kind, d->n_trunc);
+    a.target = (const T *)b->target;
+    a.gB = (d->flags & FES_TARGET_SHARED) ? 1 : d->batch;
+    a.gS = (d->flags & FES_TARGET_SHARED) ? 0 : 1;
+    a.weight = (const T *)b->weight;
+    a.lower = (const T *)b->lower;
+    a.upper = (const T *)b->upper;
+    a.params_out = (T *)b->params_out;
+    a.cost = (T *)b->cost;
+    a.grad = (T *)b->grad;
+    a.hess = (T *)b->hess;
+    a.iters = b->iters;
+    a.B = d->batch;
+    a.N = d->n_trunc;
+    a.ns = d->n_shooting;
+    a.S = d->n_steps;
+    a.scheme = d->scheme;
+    a.max_iter = o->max_iter;
+    a.p_mask = o->p_mask;
+    a.h = (T)(d->dt / d->n_steps);
+    a.dt = (T)d->dt;
+    a.tauc = (T)d->tauc;
+    a.r0_km = (T)d->r0_km;
+    a.lambda0 = (T)o->lambda0;
+    a.ftol = (T)o->ftol;
+    a.xtol = (T)o->xtol;
 }
 
 inline const char *strerror_abi(int code) {

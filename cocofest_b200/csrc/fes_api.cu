@@ -14,6 +14,11 @@ namespace fes {
     extern template int launch_shoot_kf<float, K, F>(int, const ShootArgs<float> &, cudaStream_t);
 FES_EXTERN(0, false) FES_EXTERN(0, true) FES_EXTERN(1, false) FES_EXTERN(1, true) FES_EXTERN(2, false) FES_EXTERN(2, true)
 #undef FES_EXTERN
+#define FES_EXTERN_ID(K)                                                                      \
+    extern template int launch_ident_k<double, K>(const IdentArgs<double> &, cudaStream_t);   \
+    extern template int launch_ident_k<float, K>(const IdentArgs<float> &, cudaStream_t);
+FES_EXTERN_ID(0) FES_EXTERN_ID(1) FES_EXTERN_ID(2)
+#undef FES_EXTERN_ID
 }  // namespace fes
 
 namespace {
@@ -101,6 +106,25 @@ int shoot_impl(const FesDesc *d, const FesShootBuffers *b, void *stream) {
     ShootArgs<T> a;
     fill_shoot_args<T>(d, b, c, a);
     rc = dispatch_shoot<T>(d->model_kind, d->fatigue, groups, a, s);
+    if (rc == 0) ++g_launches;
+    return rc;
+}
+
+template <typename T>
+int ident_impl(const FesDesc *d, const FesIdentBuffers *b, const FesIdentOptions *o, void *stream) {
+    int rc = check_ident(d, b, o);
+    if (rc) return rc;
+    cudaStream_t s = (cudaStream_t)stream;
+    const Carve c = carve(d, sizeof(T));
+    rc = build_tables<T>(d, b->stim_win, b->workspace, b->workspace_bytes, c, s);
+    if (rc) return rc;
+    IdentArgs<T> a;
+    fill_ident_args<T>(d, b, o, c, a);
+    switch (d->model_kind) {
+        case 0: rc = launch_ident_k<T, 0>(a, s); break;
+        case 1: rc = launch_ident_k<T, 1>(a, s); break;
+        default: rc = launch_ident_k<T, 2>(a, s); break;
+    }
     if (rc == 0) ++g_launches;
     return rc;
 }
@@ -206,6 +230,48 @@ int shoot_host_impl(const FesDesc *d, const FesShootBuffers *h, void *stream) {
     return (int)cudaStreamSynchronize(s);
 }
 
+template <typename T>
+int ident_host_impl(const FesDesc *d, const FesIdentBuffers *h, const FesIdentOptions *o, void *stream) {
+    int rc = check_ident(d, h, o);
+    if (rc) return rc;
+    if (h->stim_win == nullptr) return E_BUF;
+    cudaStream_t s = (cudaStream_t)stream;
+    const int nu = num_controls(d->model_kind, d->n_trunc), np = ident_num_params(d->model_kind);
+    const size_t B = (size_t)d->batch, ns = (size_t)d->n_shooting, N = (size_t)d->n_trunc;
+    FesDesc dd = *d;
+    dd.flags &= ~FES_TABLES_READY;
+    FesIdentBuffers g;
+    std::memset(&g, 0, sizeof(g));
+    {
+        DevPool pool(s);
+        g.params = pool.upload(h->params, sizeof(T) * FES_NP * ((d->flags & FES_PARAMS_SHARED) ? 1 : B));
+        g.x0 = pool.upload(h->x0, sizeof(T) * 2 * B);
+        g.stim_win = (const double *)pool.upload(h->stim_win, sizeof(double) * ns * N * ((d->flags & FES_WIN_SHARED) ? 1 : B));
+        if (nu) g.ctrl = pool.upload(h->ctrl, sizeof(T) * ns * nu * ((d->flags & FES_CTRL_SHARED) ? 1 : B));
+        g.target = pool.upload(h->target, sizeof(T) * (ns + 1) * ((d->flags & FES_TARGET_SHARED) ? 1 : B));
+        g.weight = pool.upload(h->weight, sizeof(T) * (ns + 1));
+        g.lower = pool.upload(h->lower, sizeof(T) * FES_NP);
+        g.upper = pool.upload(h->upper, sizeof(T) * FES_NP);
+        g.params_out = pool.alloc(sizeof(T) * FES_NP * B);
+        g.cost = pool.alloc(sizeof(T) * B);
+        g.grad = pool.alloc(sizeof(T) * np * B);
+        g.hess = pool.alloc(sizeof(T) * (np * (np + 1) / 2) * B);
+        if (h->iters) g.iters = (int32_t *)pool.alloc(sizeof(int32_t) * B);
+        g.workspace_bytes = fes_workspace_bytes(&dd, sizeof(T) == 4);
+        g.workspace = pool.alloc((size_t)g.workspace_bytes);
+        if (pool.err) return pool.err;
+        rc = ident_impl<T>(&dd, &g, o, stream);
+        if (rc) return rc;
+        pool.download(h->params_out, g.params_out, sizeof(T) * FES_NP * B);
+        pool.download(h->cost, g.cost, sizeof(T) * B);
+        pool.download(h->grad, g.grad, sizeof(T) * np * B);
+        pool.download(h->hess, g.hess, sizeof(T) * (np * (np + 1) / 2) * B);
+        if (g.iters) pool.download(h->iters, g.iters, sizeof(int32_t) * B);
+        if (pool.err) return pool.err;
+    }
+    return (int)cudaStreamSynchronize(s);
+}
+
 // ---- FMA peak probe ------------------------------------------------------------------------------
 template <typename T>
 __global__ void __launch_bounds__(256) fes_fma_probe_kernel(T *out, int iters, T m, T c) {
@@ -289,6 +355,11 @@ int fes_ivp_host_f64(const FesDesc *d, const FesIvpBuffers *b, void *s) { return
 int fes_ivp_host_f32(const FesDesc *d, const FesIvpBuffers *b, void *s) { return ivp_host_impl<float>(d, b, s); }
 int fes_shoot_host_f64(const FesDesc *d, const FesShootBuffers *b, void *s) { return shoot_host_impl<double>(d, b, s); }
 int fes_shoot_host_f32(const FesDesc *d, const FesShootBuffers *b, void *s) { return shoot_host_impl<float>(d, b, s); }
+
+int fes_identify_f64(const FesDesc *d, const FesIdentBuffers *b, const FesIdentOptions *o, void *s) { return ident_impl<double>(d, b, o, s); }
+int fes_identify_f32(const FesDesc *d, const FesIdentBuffers *b, const FesIdentOptions *o, void *s) { return ident_impl<float>(d, b, o, s); }
+int fes_identify_host_f64(const FesDesc *d, const FesIdentBuffers *b, const FesIdentOptions *o, void *s) { return ident_host_impl<double>(d, b, o, s); }
+int fes_identify_host_f32(const FesDesc *d, const FesIdentBuffers *b, const FesIdentOptions *o, void *s) { return ident_host_impl<float>(d, b, o, s); }
 
 int fes_probe_fma_peak(int is_f32, int launches, void *stream, double *tflops_out) {
     if (tflops_out == nullptr || launches < 1) return E_BUF;

@@ -121,6 +121,10 @@ FES_HD double xexp(double a) { return exp(a); }
 FES_HD float xexp(float a) { return expf(a); }
 FES_HD double xtanh(double a) { return tanh(a); }
 FES_HD float xtanh(float a) { return tanhf(a); }
+FES_HD double xsqrt(double a) { return sqrt(a); }
+FES_HD float xsqrt(float a) { return sqrtf(a); }
+FES_HD double xabs(double a) { return fabs(a); }
+FES_HD float xabs(float a) { return fabsf(a); }
 
 // reciprocal without the denormal / overflow slow path: the arguments here are products of
 // physiological quantities, (Km + Cn) * (tau1 (Km + Cn) + tau2 Cn), far from the range limits.
@@ -131,8 +135,10 @@ FES_HD double xrcp(double x) {
     double e = fma(-x, r, 1.0);
     e = fma(e, e, e);
     r = fma(r, e, r);
+#ifndef FES_RCP_SHORT
     e = fma(-x, r, 1.0);
     r = fma(r, e, r);
+#endif
     return r;
 #else
     return 1.0 / x;
@@ -280,7 +286,7 @@ FES_HD void nominal_rhs(const Traj<T> &tr, T Ee, T g, const T *x, T *k, Stage<T>
     const T A = FAT ? x[2] : tr.a_rest;
     const T t1 = FAT ? x[3] : tr.tau1_rest;
     const T km = FAT ? x[4] : tr.km_rest;
-    k[0] = (Ee - cn) * tr.inv_tauc;
+    k[0] = xfma(-tr.inv_tauc, cn, Ee);       // Ee already carries the 1/tauc factor (rk_step_scheme)
     const T s = km + cn;
     const T M = xfma(tr.tau2, cn, t1 * s);  // (tau1 + tau2 q) * s
     const T r = xrcp(s * M);
@@ -468,6 +474,7 @@ FES_HD void rk_step_scheme(const Traj<T> &tr, const Interval<T, Dirs<KIND, FAT, 
     // the two shared decaying scalars of the reduced columns obey m' = -(z / h) m: same scheme, in double
     const double zf = (double)tr.kappa * (double)h, zc = (double)tr.inv_tauc * (double)h;
     double mus = tg.mu, mun = tg.mu, nus = tg.nu, nun = tg.nu;
+    const T Etc = iv.E * tr.inv_tauc;  // Cn' = (E eps - Cn)/tauc = Etc eps - Cn/tauc
 
     static_for<0, NS>([&](auto is) {
         constexpr int s = decltype(is)::value;
@@ -478,7 +485,7 @@ FES_HD void rk_step_scheme(const Traj<T> &tr, const Interval<T, Dirs<KIND, FAT, 
         Stage<T> st;
         {
             T k[NX];
-            nominal_rhs<T, KIND, FAT, NEED>(tr, iv.E * eps, iv.g, xs, k, st);
+            nominal_rhs<T, KIND, FAT, NEED>(tr, Etc * eps, iv.g, xs, k, st);
 #pragma unroll
             for (int j = 0; j < NX; ++j) {
                 if constexpr (TB::beta(s) != 0.0) xn[j] = xfma(hb, k[j], xn[j]);

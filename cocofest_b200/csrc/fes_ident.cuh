@@ -1,0 +1,264 @@
+// fes_ident.cuh -- force-tracking cost assembly and batched Levenberg-Marquardt identification on device.
+//
+// What the reference does (one candidate at a time, on the host):
+//   - residuals r_j = F(t_j) - F_data(t_j) at all ns+1 nodes, cost = sum_j w_j r_j^2 with w_j = dt
+//     (Lagrange TRACK_STATE on "F", Node.ALL, quadratic: optimization/fes_identification_ocp.py:248-266;
+//     the data are resampled at the nodes by identification_method.py:253-278, force_at_node_in_ocp)
+//   - decision parameters a_rest, km_rest, tau1_rest, tau2 (+ pd0, pdt | ar, bs, Is, cr) with box bounds
+//     (fes_identification_ocp.py:269-299; defaults ding2003_force_parameter_identification.py:121-150,
+//     ding2007_...:105-148, hmed2018_...:103-160), fatigue models rejected (ding2003_...:196-199)
+//   - one Ipopt solve per candidate through casadi AD.
+//
+// Here: ONE thread owns one candidate for the WHOLE identification.  It integrates the two-state model with
+// the chained parameter tangents (fes_core.cuh, direction group P), folds every node's residual into the
+// cost, its gradient and the Gauss-Newton matrix J^T W J held in registers (the [ns+1] x np Jacobian is never
+// written to HBM), then iterates a bounded Levenberg-Marquardt loop (Marquardt-scaled Cholesky solve in
+// registers, projection on the box, accept / reject with lambda update) without leaving the kernel.
+// max_iter = 0 turns the same kernel into the plain cost / gradient / Gauss-Newton evaluation.
+#pragma once
+
+#include "fes_kernels.cuh"
+
+namespace fes {
+
+template <int KIND>
+struct IdentDims {
+    static constexpr int NPK = KIND == DING2003 ? 4 : (KIND == DING2007 ? 6 : 8);  // identifiable parameters
+    static constexpr int NH = NPK * (NPK + 1) / 2;                                 // upper triangle, row-major
+    // canonical parameter row of P-group column d (same order as Dirs<KIND, false, G_P>::code)
+    static constexpr int canon(int d) { return d < 4 ? d : (KIND == DING2007 ? P_PD0 + (d - 4) : P_AR + (d - 4)); }
+    static constexpr int hidx(int d, int e) { return d * NPK - d * (d - 1) / 2 + (e - d); }  // d <= e
+};
+
+template <typename T>
+struct IdentArgs {
+    const T *params; int64_t pB, pS;   // starting points: params[j*pB + b*pS]
+    const T *x0;                       // [2][B] | nullptr (rest: Cn = F = 0)
+    const T *tab; int64_t tB, tS; int row;
+    const T *eps;
+    const T *ctrl; int64_t cB, cS; int nu;
+    const T *target; int64_t gB, gS;   // force data at the nodes: target[node*gB + b*gS]
+    const T *weight;                   // [ns+1] | nullptr (every node weighs dt)
+    const T *lower, *upper;            // [NP] box of the canonical parameters | nullptr
+    T *params_out, *cost, *grad, *hess;
+    int32_t *iters;
+    int64_t B;
+    int N, ns, S, scheme, max_iter, p_mask;
+    T h, dt, tauc, r0_km, lambda0, ftol, xtol;
+};
+
+// cost, gradient and Gauss-Newton matrix of one candidate (parameters pc[NP]) -------------------------
+template <typename T, int KIND>
+FES_HD void ident_eval(const IdentArgs<T> &a, int64_t b, const T *pc, const T *eps, T &cost, T *g, T *H) {
+    using I = IdentDims<KIND>;
+    constexpr int NPK = I::NPK;
+    Traj<T> tr;
+    load_traj(tr, [&](int j) { return pc[j]; }, a.tauc, a.r0_km);
+    T x[2] = {T(0), T(0)};
+    if (a.x0 != nullptr) {
+        x[0] = a.x0[b];
+        x[1] = a.x0[a.B + b];
+    }
+    Tangent<T, KIND, false, G_P> tg;
+    tg.init();
+    cost = T(0);
+    static_for<0, NPK>([&](auto ic) { g[decltype(ic)::value] = T(0); });
+    static_for<0, I::NH>([&](auto ic) { H[decltype(ic)::value] = T(0); });
+    auto fold = [&](int node) {
+        const T w = a.weight != nullptr ? a.weight[node] : a.dt;
+        const T r = x[1] - a.target[(int64_t)node * a.gB + b * a.gS];
+        const T wr = w * r;
+        cost = xfma(wr, r, cost);
+        static_for<0, NPK>([&](auto id) {
+            constexpr int d = decltype(id)::value;
+            const T vd = tg.V[d][1];
+            g[d] = xfma(wr + wr, vd, g[d]);
+            const T wv = (w + w) * vd;
+            static_for<d, NPK>([&](auto ie) {
+                constexpr int e = decltype(ie)::value;
+                H[I::hidx(d, e)] = xfma(wv, tg.V[e][1], H[I::hidx(d, e)]);
+            });
+        });
+    };
+    fold(0);
+    for (int node = 0; node < a.ns; ++node) {
+        const T *trow = a.tab + (int64_t)node * a.row * a.tB + b * a.tS;
+        const T *crow = a.ctrl + (int64_t)node * a.nu * a.cB + b * a.cS;
+        Interval<T, NPK> iv;
+        interval_setup<T, KIND, false, G_P>(
+            tr, [&](int c) { return trow[c * a.tB]; }, [&](int c) { return crow[c * a.cB]; }, a.N, 0, iv);
+        for (int i = 0; i < a.S; ++i)
+            rk_step<T, KIND, false, G_P>(tr, iv, a.scheme, a.h, eps[2 * i], eps[2 * i + 1], eps[2 * i + 2], x, tg);
+        fold(node + 1);
+    }
+}
+
+// Marquardt-scaled step: solves (H + lambda diag(H)) delta = -g on the free parameters (p_mask: identified and
+// not held on a bound) by an in-register Cholesky factorisation.  Returns false when the matrix is not
+// numerically positive definite.
+template <typename T, int KIND>
+FES_HD bool ident_solve(const T *g, const T *H, T lambda, int p_mask, T *delta) {
+    using I = IdentDims<KIND>;
+    constexpr int NPK = I::NPK;
+    T L[I::NH];
+    T rhs[NPK];
+    static_for<0, NPK>([&](auto id) {
+        constexpr int d = decltype(id)::value;
+        const bool on = ((p_mask >> d) & 1) && H[I::hidx(d, d)] > T(0);
+        static_for<d, NPK>([&](auto ie) {
+            constexpr int e = decltype(ie)::value;
+            const bool on_e = ((p_mask >> e) & 1) && H[I::hidx(e, e)] > T(0);
+            L[I::hidx(d, e)] = (on && on_e) ? H[I::hidx(d, e)] : T(0);
+        });
+        L[I::hidx(d, d)] = on ? H[I::hidx(d, d)] * (T(1) + lambda) : T(1);
+        rhs[d] = on ? -g[d] : T(0);
+    });
+    bool ok = true;
+    // upper Cholesky H = U^T U, row by row
+    static_for<0, NPK>([&](auto id) {
+        constexpr int d = decltype(id)::value;
+        T piv = L[I::hidx(d, d)];
+        if (!(piv > T(0))) ok = false;
+        const T inv = T(1) / xsqrt(piv > T(0) ? piv : T(1));
+        static_for<d, NPK>([&](auto ie) {
+            constexpr int e = decltype(ie)::value;
+            L[I::hidx(d, e)] *= inv;
+        });
+        static_for<d + 1, NPK>([&](auto ir) {
+            constexpr int r = decltype(ir)::value;
+            static_for<r, NPK>([&](auto ie) {
+                constexpr int e = decltype(ie)::value;
+                L[I::hidx(r, e)] = xfma(-L[I::hidx(d, r)], L[I::hidx(d, e)], L[I::hidx(r, e)]);
+            });
+        });
+    });
+    // forward: U^T y = rhs
+    static_for<0, NPK>([&](auto id) {
+        constexpr int d = decltype(id)::value;
+        T s = rhs[d];
+        static_for<0, d>([&](auto ik) {
+            constexpr int k = decltype(ik)::value;
+            s = xfma(-L[I::hidx(k, d)], rhs[k], s);
+        });
+        rhs[d] = s / L[I::hidx(d, d)];
+    });
+    // backward: U delta = y
+    static_for<0, NPK>([&](auto id) {
+        constexpr int d = NPK - 1 - decltype(id)::value;
+        T s = rhs[d];
+        static_for<d + 1, NPK>([&](auto ik) {
+            constexpr int k = decltype(ik)::value;
+            s = xfma(-L[I::hidx(d, k)], delta[k], s);
+        });
+        delta[d] = s / L[I::hidx(d, d)];
+    });
+    return ok;
+}
+
+// the whole identification of candidate b ------------------------------------------------------------------
+template <typename T, int KIND>
+FES_HD void ident_candidate(const IdentArgs<T> &a, int64_t b, const T *eps) {
+    using I = IdentDims<KIND>;
+    constexpr int NPK = I::NPK;
+    constexpr int NH = I::NH;
+    T pc[NP];
+#pragma unroll
+    for (int j = 0; j < NP; ++j) pc[j] = a.params[j * a.pB + b * a.pS];
+    if (a.max_iter > 0) {  // the iteration starts inside the box
+        static_for<0, NPK>([&](auto id) {
+            constexpr int d = decltype(id)::value;
+            constexpr int j = I::canon(d);
+            if (!((a.p_mask >> d) & 1)) return;
+            if (a.lower != nullptr && pc[j] < a.lower[j]) pc[j] = a.lower[j];
+            if (a.upper != nullptr && pc[j] > a.upper[j]) pc[j] = a.upper[j];
+        });
+    }
+    T cost, g[NPK], H[NH];
+    ident_eval<T, KIND>(a, b, pc, eps, cost, g, H);
+    auto publish = [&]() {
+        a.cost[b] = cost;
+        static_for<0, NPK>([&](auto ic) { a.grad[decltype(ic)::value * a.B + b] = g[decltype(ic)::value]; });
+        static_for<0, NH>([&](auto ic) { a.hess[decltype(ic)::value * a.B + b] = H[decltype(ic)::value]; });
+    };
+    publish();
+    T cur = cost;
+    T lambda = a.lambda0;
+    int evals = 1;
+    for (int it = 0; it < a.max_iter; ++it) {
+        if (!(cur > T(0)) || !(lambda < T(1e15))) break;  // exact fit, NaN start, or no acceptable step left
+        // current gradient / Gauss-Newton matrix live in the output arrays (registers hold the trial ones)
+        static_for<0, NPK>([&](auto ic) { g[decltype(ic)::value] = a.grad[decltype(ic)::value * a.B + b]; });
+        static_for<0, NH>([&](auto ic) { H[decltype(ic)::value] = a.hess[decltype(ic)::value * a.B + b]; });
+        // active set: a parameter sitting on a bound whose gradient pushes it further out is held for this step
+        int free_mask = a.p_mask;
+        static_for<0, NPK>([&](auto id) {
+            constexpr int d = decltype(id)::value;
+            constexpr int j = I::canon(d);
+            if (a.lower != nullptr && pc[j] <= a.lower[j] && g[d] > T(0)) free_mask &= ~(1 << d);
+            if (a.upper != nullptr && pc[j] >= a.upper[j] && g[d] < T(0)) free_mask &= ~(1 << d);
+        });
+        T delta[NPK];
+        if (!ident_solve<T, KIND>(g, H, lambda, free_mask, delta)) {
+            lambda *= T(10);
+            continue;
+        }
+        T pt[NP];
+#pragma unroll
+        for (int j = 0; j < NP; ++j) pt[j] = pc[j];
+        T step = T(0);
+        static_for<0, NPK>([&](auto id) {
+            constexpr int d = decltype(id)::value;
+            constexpr int j = I::canon(d);
+            T v = pc[j] + delta[d];
+            if (a.lower != nullptr) v = v < a.lower[j] ? a.lower[j] : v;
+            if (a.upper != nullptr) v = v > a.upper[j] ? a.upper[j] : v;
+            const T rel = xabs(v - pc[j]) / (xabs(pc[j]) + T(1e-30));
+            step = rel > step ? rel : step;
+            pt[j] = v;
+        });
+        if (!(step > T(0))) break;  // pinned on the box in every identified direction
+        ident_eval<T, KIND>(a, b, pt, eps, cost, g, H);
+        ++evals;
+        if (cost < cur) {
+            const T gain = cur - cost;
+#pragma unroll
+            for (int j = 0; j < NP; ++j) pc[j] = pt[j];
+            publish();
+            const bool done = gain <= a.ftol * cur || step <= a.xtol;
+            cur = cost;
+            lambda = lambda * T(1.0 / 3.0);
+            if (lambda < T(1e-12)) lambda = T(1e-12);
+            if (done) break;
+        } else {
+            lambda *= T(4);
+        }
+    }
+#pragma unroll
+    for (int j = 0; j < NP; ++j) a.params_out[j * a.B + b] = pc[j];
+    if (a.iters != nullptr) a.iters[b] = evals;
+}
+
+#if defined(__CUDACC__)
+
+template <typename T, int KIND>
+__global__ void __launch_bounds__(BLOCK) fes_ident_kernel(const IdentArgs<T> a) {
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    T *s_eps = reinterpret_cast<T *>(smem_raw);
+    for (int i = threadIdx.x; i < 2 * a.S + 1; i += BLOCK) s_eps[i] = a.eps[i];
+    __syncthreads();
+    const int64_t b = (int64_t)blockIdx.x * BLOCK + threadIdx.x;
+    if (b >= a.B) return;
+    ident_candidate<T, KIND>(a, b, s_eps);
+}
+
+template <typename T, int KIND>
+int launch_ident_k(const IdentArgs<T> &a, cudaStream_t s) {
+    const unsigned grid = (unsigned)((a.B + BLOCK - 1) / BLOCK);
+    const size_t smem = ((2 * a.S + 1 + 3) & ~3) * sizeof(T);
+    fes_ident_kernel<T, KIND><<<grid, BLOCK, smem, s>>>(a);
+    return (int)cudaGetLastError();
+}
+
+#endif  // __CUDACC__
+
+}  // namespace fes

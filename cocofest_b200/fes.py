@@ -22,8 +22,8 @@ import torch
 
 from . import _lib
 from ._lib import (FES_CTRL_SHARED, FES_DING2003, FES_DING2007, FES_DIR_P, FES_DIR_PF, FES_DIR_U, FES_DIR_W,
-                   FES_DIR_X0, FES_HMED2018, FES_NP, FES_PARAMS_SHARED, FES_TILE, FES_WIN_SHARED, PARAM_INDEX,
-                   PARAM_NAMES, FesDesc, FesIvpBuffers, FesShootBuffers)
+                   FES_DIR_X0, FES_HMED2018, FES_NP, FES_PARAMS_SHARED, FES_TARGET_SHARED, FES_TILE, FES_WIN_SHARED,
+                   PARAM_INDEX, PARAM_NAMES, FesDesc, FesIdentBuffers, FesIdentOptions, FesIvpBuffers, FesShootBuffers)
 
 PAD_TIME = -10000000  # ding2003.py:396
 PAD_INTENSITY = 50  # hmed2018.py:315
@@ -355,6 +355,114 @@ def shoot(kind, fatigue, params, X, win, dt, n_steps=10, ctrl=None, scheme=4, wa
     o += cp
     Jw = J[:, :, o:o + N] if cw else None
     return ShootResult(G, Phi, Jx, Ju, Jp, Jw, tuple(np_cols))
+
+
+@dataclass
+class IdentResult:
+    params: torch.Tensor        # [14, B]  identified canonical parameter vectors
+    cost: torch.Tensor          # [B]      sum_j w_j (F(t_j) - target_j)^2 at params
+    grad: torch.Tensor          # [np, B]  d cost / d P-column
+    hess: torch.Tensor          # [np(np+1)/2, B]  Gauss-Newton matrix 2 J^T W J, upper triangle row-major
+    evaluations: torch.Tensor   # [B] int32
+    columns: tuple              # names of the np P-columns
+
+    def hessian(self) -> torch.Tensor:
+        """Dense symmetric [np, np, B] view of ``hess``."""
+        n = len(self.columns)
+        iu = torch.triu_indices(n, n, device=self.hess.device)
+        H = torch.zeros((n, n, self.hess.shape[-1]), dtype=self.hess.dtype, device=self.hess.device)
+        H[iu[0], iu[1]] = self.hess
+        H[iu[1], iu[0]] = self.hess
+        return H
+
+    def best(self) -> int:
+        """Index of the candidate with the lowest finite cost (multi-start selection)."""
+        c = torch.where(torch.isfinite(self.cost), self.cost, torch.full_like(self.cost, float("inf")))
+        return int(torch.argmin(c).item())
+
+
+def identify(kind, params, win, dt, target, n_steps=10, ctrl=None, identify=None, lower=None, upper=None, weight=None,
+             x0=None, max_iter=50, lambda0=1e-3, ftol=1e-12, xtol=1e-12, scheme=4, t_start=0.0, tauc=None,
+             r0_km=R0_KM_RELATIONSHIP, dtype=None) -> IdentResult:
+    """Force-tracking cost / gradient / Gauss-Newton matrix and bounded Levenberg-Marquardt identification of
+    B candidates at once (one GPU thread per candidate, the whole loop on device).
+
+    Replaces, for the two-state models, ``OcpFesId`` + one Ipopt solve per candidate
+    (optimization/fes_identification_ocp.py:248-299): cost = sum over ALL ns+1 nodes of w_j (F(t_j) - target_j)^2,
+    w_j = dt by default (Lagrange TRACK_STATE on "F", Node.ALL, quadratic).
+
+    params [14, B] (or [14], needs a per-candidate ``target``): starting points;  target [ns+1] | [ns+1, B];
+    identify: names of the parameters to identify (default: all P-columns of the model, ``P_COLUMNS[kind]``);
+    lower / upper: dict name -> bound, or [14] tensors;  max_iter = 0 only evaluates.
+    """
+    target = torch.as_tensor(target)
+    params = torch.as_tensor(params)
+    lead = params if params.dim() == 2 else (target if target.dim() == 2 else None)
+    if lead is None:
+        raise ValueError("either params [14,B] or target [ns+1,B] must carry the batch axis")
+    device, dtype, B, N, flags, params, win, ctrl = _common(kind, False, params, win, ctrl, lead, dtype)
+    target = _prep(target, dtype, device)
+    ns = target.shape[0] - 1
+    if target.dim() == 1:
+        flags |= FES_TARGET_SHARED
+    elif target.shape != (ns + 1, B):
+        raise ValueError("target must be [ns+1] or [ns+1, B]")
+    if ns < 1 or win.shape[0] < ns or (ctrl is not None and ctrl.shape[0] < ns):
+        raise ValueError("stim window / controls have fewer rows than the target has intervals")
+    cols = P_COLUMNS[kind]
+    names = cols if identify is None else tuple(identify)
+    alias = {"a_scale": "a_rest", "a_rest": "a_scale"}
+    mask = 0
+    for n in names:
+        if n in cols:
+            mask |= 1 << cols.index(n)
+        elif alias.get(n) in cols:
+            mask |= 1 << cols.index(alias[n])
+        else:
+            raise ValueError(f"{n} is not identifiable for this model; available: {cols}")
+
+    def bounds(b, fill):
+        if b is None:
+            return None
+        if isinstance(b, dict):
+            v = torch.full((FES_NP,), fill, dtype=torch.float64)
+            for k, val in b.items():
+                v[PARAM_INDEX[k]] = val
+            b = v
+        return _prep(b, dtype, device)
+
+    lower, upper = bounds(lower, -float("inf")), bounds(upper, float("inf"))
+    weight = _prep(weight, dtype, device)
+    if weight is not None and weight.shape != (ns + 1,):
+        raise ValueError("weight must be [ns+1]")
+    x0 = _prep(x0, dtype, device)
+    if x0 is not None and x0.shape != (2, B):
+        raise ValueError("x0 must be [2, B]")
+    n_p = len(cols)
+    desc = _desc(kind, False, scheme, N, ns, n_steps, FES_DIR_P, flags, B, dt, t_start, tauc, r0_km)
+    out_p = _empty((FES_NP, B), dtype, device)
+    out_c = _empty((B,), dtype, device)
+    out_g = _empty((n_p, B), dtype, device)
+    out_h = _empty((n_p * (n_p + 1) // 2, B), dtype, device)
+    out_i = _empty((B,), torch.int32, device)
+    opt = FesIdentOptions(int(max_iter), int(mask), float(lambda0), float(ftol), float(xtol))
+    buf = FesIdentBuffers(_ptr(params), _ptr(x0), _ptr(win), _ptr(ctrl), _ptr(target), _ptr(weight), _ptr(lower),
+                          _ptr(upper), _ptr(out_p), _ptr(out_c), _ptr(out_g), _ptr(out_h), _ptr(out_i), None, 0)
+    L = _lib.lib()
+    is32 = dtype == torch.float32
+    if device.type == "cuda":
+        with torch.cuda.device(device):
+            wbytes = L.fes_workspace_bytes(ctypes.byref(desc), int(is32))
+            ws = torch.empty(max(int(wbytes), 1), dtype=torch.uint8, device=device)
+            buf.workspace, buf.workspace_bytes = ws.data_ptr(), wbytes
+            fn = L.fes_identify_f32 if is32 else L.fes_identify_f64
+            _lib.check(fn(ctypes.byref(desc), ctypes.byref(buf), ctypes.byref(opt), ctypes.c_void_p(_stream_ptr(device))),
+                       "fes_identify")
+            ws.record_stream(torch.cuda.current_stream(device))
+    else:
+        fn = L.fes_identify_host_f32 if is32 else L.fes_identify_host_f64
+        _lib.check(fn(ctypes.byref(desc), ctypes.byref(buf), ctypes.byref(opt), None), "fes_identify_host")
+    return IdentResult(out_p, out_c, out_g, out_h, out_i, cols)
 
 
 def probe_fma_peak(is_f32=False, launches=5, device=None) -> float:

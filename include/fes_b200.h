@@ -79,6 +79,7 @@ extern "C" {
 #define FES_WIN_SHARED 2    /* stim_win is [rows][N] instead of [rows][N][B]              */
 #define FES_CTRL_SHARED 4   /* ctrl is [ns][nu] instead of [ns][nu][B]                    */
 #define FES_TABLES_READY 8  /* workspace already holds the tables of this (desc, stim_win) */
+#define FES_TARGET_SHARED 16 /* identify: target is [ns+1] instead of [ns+1][B]              */
 
 typedef struct FesDesc {
     int32_t abi_version; /* FES_ABI_VERSION */
@@ -130,6 +131,35 @@ typedef struct FesShootBuffers {
     int64_t workspace_bytes;
 } FesShootBuffers;
 
+/* Buffers of one identify call (two-state models only: the reference rejects fatigue models for
+ * identification, identification/ding2003_force_parameter_identification.py:196-199).
+ * Column d of the parameter group P is a_rest|a_scale, km_rest, tau1_rest, tau2 [, pd0, pdt | ar, bs, Is, cr]. */
+typedef struct FesIdentBuffers {
+    const void *params;     /* [FES_NP][B] | [FES_NP]  starting point of every candidate (all 14 rows)          */
+    const void *x0;         /* [2][B] | NULL = rest (Cn = F = 0)                                               */
+    const double *stim_win; /* [>=ns][N][B] | [>=ns][N]                                                        */
+    const void *ctrl;       /* [ns][nu][B] | [ns][nu] | NULL when nu = 0                                       */
+    const void *target;     /* [ns+1][B] | [ns+1]  force data resampled at the nodes (force_at_node_in_ocp)    */
+    const void *weight;     /* [ns+1] node weights | NULL = dt each (Lagrange TRACK_STATE, Node.ALL)           */
+    const void *lower;      /* [FES_NP] lower bounds of the canonical parameters | NULL                        */
+    const void *upper;      /* [FES_NP] upper bounds | NULL                                                    */
+    void *params_out;       /* [FES_NP][B] identified parameters (rows that are not identified are copied)     */
+    void *cost;             /* [B]  sum_j w_j (F(t_j) - target_j)^2 at params_out                              */
+    void *grad;             /* [np][B]  d cost / d P-column at params_out                                      */
+    void *hess;             /* [np(np+1)/2][B]  Gauss-Newton matrix 2 J^T W J, upper triangle row-major        */
+    int32_t *iters;         /* [B] number of cost evaluations spent | NULL                                     */
+    void *workspace;
+    int64_t workspace_bytes;
+} FesIdentBuffers;
+
+typedef struct FesIdentOptions {
+    int32_t max_iter; /* Levenberg-Marquardt iterations; 0 = evaluate cost / gradient / Gauss-Newton matrix only */
+    int32_t p_mask;   /* bit d set = P-column d is identified (key_parameter_to_identify)                      */
+    double lambda0;   /* initial damping (Marquardt scaling: H + lambda diag(H)); e.g. 1e-3                    */
+    double ftol;      /* stop when an accepted step lowers the cost by less than ftol * cost                   */
+    double xtol;      /* stop when an accepted step moves every parameter by less than xtol (relative)         */
+} FesIdentOptions;
+
 int fes_version(void);
 const char *fes_strerror(int code);
 
@@ -147,11 +177,19 @@ int fes_ivp_f32(const FesDesc *desc, const FesIvpBuffers *buf, void *stream);
 int fes_shoot_f64(const FesDesc *desc, const FesShootBuffers *buf, void *stream);
 int fes_shoot_f32(const FesDesc *desc, const FesShootBuffers *buf, void *stream);
 
+/* Force-tracking cost (fes_identification_ocp.py:248-266) with its gradient and Gauss-Newton matrix, and the
+ * bounded Levenberg-Marquardt identification of the P-group parameters (fes_identification_ocp.py:269-299), one
+ * thread per candidate, whole loop on device.  desc->dirs must be FES_DIR_P, desc->fatigue 0. */
+int fes_identify_f64(const FesDesc *desc, const FesIdentBuffers *buf, const FesIdentOptions *opt, void *stream);
+int fes_identify_f32(const FesDesc *desc, const FesIdentBuffers *buf, const FesIdentOptions *opt, void *stream);
+
 /* Same calls with HOST buffers (workspace fields ignored): H2D, kernels, D2H, stream synchronised. */
 int fes_ivp_host_f64(const FesDesc *desc, const FesIvpBuffers *host_buf, void *stream);
 int fes_ivp_host_f32(const FesDesc *desc, const FesIvpBuffers *host_buf, void *stream);
 int fes_shoot_host_f64(const FesDesc *desc, const FesShootBuffers *host_buf, void *stream);
 int fes_shoot_host_f32(const FesDesc *desc, const FesShootBuffers *host_buf, void *stream);
+int fes_identify_host_f64(const FesDesc *desc, const FesIdentBuffers *host_buf, const FesIdentOptions *opt, void *stream);
+int fes_identify_host_f32(const FesDesc *desc, const FesIdentBuffers *host_buf, const FesIdentOptions *opt, void *stream);
 
 /* Roofline denominators measured on the device the caller made current: runs `launches` launches of a
  * register-only FMA kernel on `stream` and returns the best FMA-flop rate (2 flop per FMA) in TFLOP/s. */

@@ -126,6 +126,25 @@ def main():
         print(json.dumps(line("4: Hmed2018 identification candidates, F at 21 nodes + d F/d 8 parameters",
                               B * ns * S, ms, 2, 8, ob, (p.numel() + x0.numel()) * esz, peak, args.dtype,
                               {"batch": B, "n_shooting": ns, "columns": list(out.columns)})), flush=True)
+        # the same candidates through the fused identification kernel: cost + gradient + Gauss-Newton matrix folded in
+        # registers (no [21 x 8] Jacobian in HBM), then 10 Levenberg-Marquardt iterations on device
+        F_true = fes.ivp(fes.FES_HMED2018, False, torch.tensor(fes.default_params(fes.FES_HMED2018), device=dev).to(dt_t),
+                         x0[:, :1].contiguous(), win, proto["dt"], n_steps=S, ctrl=ctrl, n_shooting=ns, trace="nodes", dtype=dt_t)
+        target = F_true.trace[:, 1, 0].contiguous()
+        lo = {k: v[0] for k, v in protocols.HMED_BOUNDS.items()}
+        hi = {k: v[1] for k, v in protocols.HMED_BOUNDS.items()}
+        for iters in (0, 10):
+            fn = lambda: fes.identify(fes.FES_HMED2018, p, win, proto["dt"], target, n_steps=S, ctrl=ctrl, lower=lo, upper=hi,
+                                      max_iter=iters, dtype=dt_t)
+            out, ms = timed(fn, args.steps, args.warmup, flush)
+            evals = int(out.evaluations.sum().item())
+            ob = (out.params.numel() + out.cost.numel() + out.grad.numel() + out.hess.numel()) * esz
+            print(json.dumps(line(f"4{'b' if iters == 0 else 'c'}: Hmed2018 fes_identify, max_iter={iters} "
+                                  "(cost + gradient + Gauss-Newton matrix folded on device" + (", LM loop on device)" if iters else ")"),
+                                  evals * ns * S, ms, 2, 8, ob, (p.numel() + x0.numel()) * esz, peak, args.dtype,
+                                  {"batch": B, "n_shooting": ns, "evaluations": evals,
+                                   "median_cost": float(out.cost.median().item()), "best_cost": float(out.cost[out.best()].item())})),
+                  flush=True)
         del out, p, x0
 
     if 5 in wanted:

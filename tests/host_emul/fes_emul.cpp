@@ -210,6 +210,40 @@ int shoot_impl(const FesDesc *d, const FesShootBuffers *b) {
     fill_shoot_args<T>(d, b, c, a);
     return disp_shoot<T>(d->model_kind, d->fatigue, groups, a);
 }
+template <typename T>
+int ident_impl(const FesDesc *d, const FesIdentBuffers *b, const FesIdentOptions *o) {
+    int rc = check_ident(d, b, o);
+    if (rc) return rc;
+    const Carve c = carve(d, sizeof(T));
+    if (!b->workspace || b->workspace_bytes < (int64_t)c.total) return E_WORKSPACE;
+    if (!(d->flags & FES_TABLES_READY)) {
+        if (!b->stim_win) return E_BUF;
+        tables_cpu<T>(d, b->stim_win, c, b->workspace);
+    }
+    IdentArgs<T> a;
+    fill_ident_args<T>(d, b, o, c, a);
+    for (int64_t i = 0; i < a.B; ++i) {
+        switch (d->model_kind) {
+            case 0: ident_candidate<T, 0>(a, i, a.eps); break;
+            case 1: ident_candidate<T, 1>(a, i, a.eps); break;
+            default: ident_candidate<T, 2>(a, i, a.eps); break;
+        }
+    }
+    return 0;
+}
+template <typename T>
+int ident_host(const FesDesc *d, const FesIdentBuffers *b, const FesIdentOptions *o) {
+    if (!d || !b) return E_DESC;
+    FesDesc dd = *d;
+    dd.flags &= ~FES_TABLES_READY;
+    const int64_t wb = fes_workspace_bytes(&dd, sizeof(T) == 4);
+    if (wb < 0) return E_SIZE;
+    std::vector<char> ws((size_t)wb + 16);
+    FesIdentBuffers bb = *b;
+    bb.workspace = ws.data();
+    bb.workspace_bytes = wb;
+    return ident_impl<T>(&dd, &bb, o);
+}
 }  // namespace
 
 extern "C" {
@@ -249,6 +283,10 @@ HOST_VARIANT(fes_ivp_host_f64, ivp_impl, double, FesIvpBuffers)
 HOST_VARIANT(fes_ivp_host_f32, ivp_impl, float, FesIvpBuffers)
 HOST_VARIANT(fes_shoot_host_f64, shoot_impl, double, FesShootBuffers)
 HOST_VARIANT(fes_shoot_host_f32, shoot_impl, float, FesShootBuffers)
+int fes_identify_f64(const FesDesc *d, const FesIdentBuffers *b, const FesIdentOptions *o, void *) { return ident_impl<double>(d, b, o); }
+int fes_identify_f32(const FesDesc *d, const FesIdentBuffers *b, const FesIdentOptions *o, void *) { return ident_impl<float>(d, b, o); }
+int fes_identify_host_f64(const FesDesc *d, const FesIdentBuffers *b, const FesIdentOptions *o, void *) { return ident_host<double>(d, b, o); }
+int fes_identify_host_f32(const FesDesc *d, const FesIdentBuffers *b, const FesIdentOptions *o, void *) { return ident_host<float>(d, b, o); }
 int fes_probe_fma_peak(int, int, void *, double *) { return E_DESC; }
 int64_t fes_launch_count(void) { return 0; }
 int fes_is_host_emulation(void) { return 1; }
