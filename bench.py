@@ -27,9 +27,23 @@ METRIC = "fatigue_ode_trajectory_steps_per_s_with_sensitivities"
 UNIT = "trajectory-steps/s"
 
 
-def flop_alg_per_step(nx=5, n_dir=5):
-    """4*(24 + 8*[n_dir>0] + 23*n_dir) + 13*nx*(1+n_dir)  (+,-,*,/ = 1, FMA = 2, exp = 1)."""
+def flop_survey_per_step(nx=5, n_dir=5):
+    """SURVEY.md section 8d, DENSE tangent formulation: 4*(24 + 8*[n_dir>0] + 23*n_dir) + 13*nx*(1+n_dir)
+    (+,-,*,/ = 1, FMA = 2, exp = 1) = 978 for the fatigue model with the 5 x0 columns."""
     return 4 * (24 + (8 if n_dir else 0) + 23 * n_dir) + 13 * nx * (1 + n_dir)
+
+
+def flop_alg_per_step():
+    """ALGORITHMIC flops of one RK4 trajectory-step of the kernel's own (reduced) formulation, Ding2003 + fatigue with
+    the 5 x0 columns -- DESIGN.md section 4 derives it line by line (+,-,*,reciprocal = 1, FMA = 2):
+      nominal stage   1 (E eps) + 27 (RHS) + 11 (Jacobian entries incl. cW)      = 39   x 4 stages = 156
+      nominal update  5 states x (2 FMA x 3 stages + 1 FMA)                                       =  70
+      shared modes    2 scalars x (3 stage FMAs + 4 update FMAs)                                  =  28
+      reduced column  stage: 5 (vF row; 3 for the F0 column) + 2 (W row); update 2 x 7 FMA = 28
+                      -> 56 x 4 columns + 48 (F0)                                                  = 272
+    Total 526.  It is lower than SURVEY 8d's 978 because the fatigue block of every tangent column collapses
+    to one scalar W (fes_core.cuh, dir_reduced); the survey figure is reported beside it."""
+    return 156 + 70 + 28 + 272
 
 
 class ClockSampler(threading.Thread):
@@ -279,9 +293,19 @@ def main():
                "api": "cocofest_b200.fes.ivp on pinned host tensors -> fes_ivp_host_f64 (C ABI)"}
 
     # ---- roofline of the dominant kernel (fes_ivp_kernel<double, ding2003, fatigue, X0>) -----------------
-    flop = flop_alg_per_step(5, 5)
+    flop = flop_alg_per_step()
     kernel_s = statistics.mean(kern_ms) * 1e-3
     achieved = flop * units_per_step / kernel_s / 1e12
+    static = {}
+    try:  # static SASS count of the RK4 path + dram traffic of one ncu --set full capture (scripts/sass_count.py, profiles/)
+        static = json.loads((ROOT / "profiles" / "r01_ivp_x0_static.json").read_text())
+    except Exception:
+        pass
+    inst = static.get("fp64_inst_per_rk4_step")
+    traffic = None
+    cap = static.get("ncu_full_capture", {})
+    if cap.get("batch") == B and cap.get("final_time_s") == args.final_time:
+        traffic = cap.get("dram_bytes")
     hbm_bytes = (params_d.numel() + 2 * x0_d.numel() + 25 * B + (ns + 1) * 5 * trace_B) * 8
     peaks = {}
     try:
@@ -290,9 +314,17 @@ def main():
         pass
     roofline = {
         "bound": "fp64", "achieved": achieved, "peak": fp64_peak, "unit": "TFLOP/s", "frac": achieved / fp64_peak if fp64_peak else None,
-        "traffic": None,
+        "traffic": traffic,
         "kernel": "fes_ivp_kernel<double, DING2003, fatigue, X0>", "kernel_ms": statistics.mean(kern_ms),
         "flop_alg_per_trajectory_step": flop,
+        "survey_dense_formulation": {"flop_per_trajectory_step": flop_survey_per_step(5, 5),
+                                     "equivalent_tflops": flop_survey_per_step(5, 5) * units_per_step / kernel_s / 1e12,
+                                     "note": "SURVEY 8d counts the dense 5-component tangent; the kernel propagates the "
+                                             "exact same tangent through 2 components per column"},
+        "fp64_pipe": None if not inst else {
+            "inst_per_trajectory_step": inst, "issue_rate_ginst_s": inst * units_per_step / kernel_s / 1e9,
+            "peak_ginst_s": fp64_peak * 1e3 / 2, "frac": inst * units_per_step / kernel_s / 1e9 / (fp64_peak * 1e3 / 2),
+            "note": "DFMA+DMUL+DADD of the RK4 path counted in the shipped SASS; every one occupies a DFMA issue slot"},
         "peak_source": "DFMA probe (fes_probe_fma_peak) measured in this run on this GPU; MEASURED_PEAKS.json holds no fp64 figure",
         "hbm": {"algorithmic_bytes": hbm_bytes, "achieved_gbs": hbm_bytes / kernel_s / 1e9, "peak_gbs": peaks.get("hbm_gbs"),
                 "note": "state, parameters and tangents stay in registers: HBM is idle by design"},

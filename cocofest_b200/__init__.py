@@ -20,10 +20,17 @@ from .models import (
 from .ode_solver import OdeSolver
 from .ivp_fes import IvpFes
 from .ocp_fes import OcpFes, FesShooting
+from .identification import (
+    DingModelFrequencyForceParameterIdentification,
+    DingModelPulseIntensityFrequencyForceParameterIdentification,
+    DingModelPulseWidthFrequencyForceParameterIdentification,
+)
 
 __all__ = [
     "fes", "FesModel", "ModelMaker", "OdeSolver", "IvpFes", "OcpFes", "FesShooting",
     "DingModelFrequency", "DingModelFrequencyWithFatigue",
     "DingModelPulseWidthFrequency", "DingModelPulseWidthFrequencyWithFatigue",
     "DingModelPulseIntensityFrequency", "DingModelPulseIntensityFrequencyWithFatigue",
+    "DingModelFrequencyForceParameterIdentification", "DingModelPulseWidthFrequencyForceParameterIdentification",
+    "DingModelPulseIntensityFrequencyForceParameterIdentification",
 ]

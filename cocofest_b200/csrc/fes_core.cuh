@@ -128,6 +128,7 @@ FES_HD float xabs(float a) { return fabsf(a); }
 
 // reciprocal without the denormal / overflow slow path: the arguments here are products of
 // physiological quantities, (Km + Cn) * (tau1 (Km + Cn) + tau2 Cn), far from the range limits.
+// MUFU.RCP64H seeds ~20 bits; r (1 + e + e^2) leaves a relative error ~e^3 < 2^-58, below one ulp.
 FES_HD double xrcp(double x) {
 #if defined(__CUDA_ARCH__)
     double r;
@@ -135,7 +136,7 @@ FES_HD double xrcp(double x) {
     double e = fma(-x, r, 1.0);
     e = fma(e, e, e);
     r = fma(r, e, r);
-#ifndef FES_RCP_SHORT
+#ifdef FES_RCP_LONG  // a second Newton step: measured no change of any parity figure (profiles/r01_rcp_short_margin.txt)
     e = fma(-x, r, 1.0);
     r = fma(r, e, r);
 #endif

@@ -241,7 +241,7 @@ FES_HD void ident_candidate(const IdentArgs<T> &a, int64_t b, const T *eps) {
 #if defined(__CUDACC__)
 
 template <typename T, int KIND>
-__global__ void __launch_bounds__(BLOCK) fes_ident_kernel(const IdentArgs<T> a) {
+__global__ void __launch_bounds__(BLOCK, 2) fes_ident_kernel(const IdentArgs<T> a) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     T *s_eps = reinterpret_cast<T *>(smem_raw);
     for (int i = threadIdx.x; i < 2 * a.S + 1; i += BLOCK) s_eps[i] = a.eps[i];

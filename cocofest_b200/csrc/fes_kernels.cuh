@@ -21,21 +21,24 @@
 
 namespace fes {
 
-// launch shape: tuned on a B200 (scripts/tune_ivp.py, profiles/r01_tune_ivp.txt); overridable for that sweep only
+// launch shape: tuned on a B200 (scripts/build_variants.sh + scripts/gpu_round1_d.sh, profiles/r01_tune_ivp_d.txt);
+// overridable for that sweep only
 #ifndef FES_BLOCK
-#define FES_BLOCK 128
+#define FES_BLOCK 64
 #endif
 constexpr int BLOCK = FES_BLOCK;
 // Resident blocks per SM the compiler must make room for.  The fp64 fatigue kernels whose columns are all
-// "reduced" (fes_core.cuh) need ~185-200 registers unconstrained = 2 blocks/SM; capping them at 168 registers
-// (3 blocks = 12 warps/SM) costs ~60 bytes of spill and measured +7 % on a B200 (profiles/r01_tune_ivp.txt).
+// "reduced" (fes_core.cuh) take ~188 registers when unconstrained.  Asking for 5 blocks of 64 threads (a cap of
+// 204 registers) makes ptxas settle on 162 registers = 6 resident blocks = 12 warps/SM with a schedule that
+// measured 4.95e10 trajectory-steps/s on a B200, against 4.45e10 for the 170-register cap of (128, 3) or (64, 6)
+// and 4.38e10 unconstrained (profiles/r01_tune_ivp_d.txt).
 template <typename T, int KIND, bool FAT, int GROUPS>
 constexpr int min_blocks() {
 #ifdef FES_MIN_BLOCKS
     return FES_MIN_BLOCKS;
 #else
     constexpr bool red = FAT && (GROUPS == G_X0 || GROUPS == G_U || GROUPS == G_W || (GROUPS == (G_X0 | G_U) && KIND == DING2007));
-    return (sizeof(T) == 8 && red) ? 3 : 2;
+    return (sizeof(T) == 8 && red) ? 5 : 2;
 #endif
 }
 #define FES_LAUNCH_BOUNDS __launch_bounds__(BLOCK, (min_blocks<T, KIND, FAT, GROUPS>()))
