@@ -137,3 +137,84 @@ class FesShooting:
             for s, src in enumerate(idx):
                 U[k, N - len(idx) + s] = pi[src]
         return U.to(self.device)
+
+
+class FesNmpcBatch:
+    """Window carry-over and warm-start shifting of the cyclic NMPC for B concurrent scenarios, on device tensors.
+
+    Reference (one scenario, Python objects rebuilt every cycle): ``FesNmpc.update_stim``
+    (optimization/fes_nmpc.py:69-85: the last ``sum_stim_truncation`` pulses of the horizon, shifted back by the
+    phase time, become ``previous_stim`` of a NEW model whose window is rebuilt),
+    ``advance_window_bounds_states`` / ``advance_window_initial_guess_states`` (:44-52, bioptim
+    MultiCyclicNonlinearModelPredictiveControl: the state at frame ``n_cycles_to_advance * cycle_len`` becomes the
+    fixed initial state, the remaining frames shift to the front and the tail repeats the last cycle) and
+    ``initialize_frames_and_parameters`` (:33-42).  Here the horizon's window table is built once per distinct
+    ``previous_stim`` (the first horizon uses the model's own, every later one the carried pulses -- identical from
+    the second horizon on because the stimulation train is periodic), and the shifts are index operations on
+    ``[frames, nx, B]`` / ``[frames, nu, B]`` tensors: no Python object per scenario, no rebuild per cycle.
+    """
+
+    def __init__(self, model, cycle_duration, n_cycles_simultaneous=1, n_cycles_to_advance=1, ode_solver=None,
+                 device=None, dtype=torch.float64):
+        if n_cycles_to_advance < 1 or n_cycles_to_advance > n_cycles_simultaneous:
+            raise ValueError("n_cycles_to_advance must lie in 1..n_cycles_simultaneous")
+        self.model = model
+        self.cycle_duration = cycle_duration
+        self.n_cycles_simultaneous = n_cycles_simultaneous
+        self.n_cycles_to_advance = n_cycles_to_advance
+        self.final_time = cycle_duration * n_cycles_simultaneous
+        self.n_shooting = OcpFes.prepare_n_shooting(model.stim_time, self.final_time)
+        if self.n_shooting % n_cycles_simultaneous:
+            raise ValueError("the stimulation train must repeat identically in every simultaneous cycle")
+        self.cycle_len = self.n_shooting // n_cycles_simultaneous
+        self.device = torch.device(device) if device is not None else torch.device("cuda")
+        solver = ode_solver if ode_solver is not None else OdeSolver.RK4(1)  # fes_ocp_nmpc_cyclic.py:40
+        self.first = FesShooting(model, self.final_time, self.n_shooting, solver, device=self.device, dtype=dtype)
+        self.shooting = self.first
+        self.horizon = 0
+
+    def update_stim(self):
+        """fes_nmpc.py:69-85 -- carried pulses of the finished horizon become previous_stim of the next."""
+        N = self.model.sum_stim_truncation
+        shift = self.cycle_duration * self.n_cycles_to_advance
+        # pulses of the current horizon (and its own previous ones) that precede the next horizon's start
+        pool = [t for t in self.model.previous_stim["time"] if t > _fes.PAD_TIME] + list(self.model.stim_time)
+        carried = [t - shift for t in pool if t - shift < 0][-N:]
+        nxt = type(self.model)(previous_stim={"time": carried}, stim_time=list(self.model.stim_time), sum_stim_truncation=N)
+        for key in self.model.identifiable_parameters:
+            setattr(nxt, key, getattr(self.model, key))
+        self.model = nxt
+        self.shooting = FesShooting(nxt, self.final_time, self.n_shooting, OdeSolverLike(self.first.scheme, self.first.n_steps),
+                                    device=self.device, dtype=self.first.dtype)
+        self.horizon += 1
+        return carried
+
+    def advance(self, X, U=None):
+        """Shifts the solved horizon to warm-start the next one.
+
+        X [ns+1, nx, B], U [ns, nu, B] -> (x_start [nx, B], X_guess, U_guess): frame ``n_cycles_to_advance * cycle_len``
+        becomes node 0 (its value is also returned as the fixed initial state); the tail repeats the last cycle."""
+        adv = self.n_cycles_to_advance * self.cycle_len
+        ns = self.n_shooting
+        idx = torch.arange(ns + 1, device=X.device) + adv
+        over = idx > ns
+        idx = torch.where(over, idx - self.cycle_len * torch.div(idx - ns + self.cycle_len - 1, self.cycle_len, rounding_mode="floor"), idx)
+        Xn = X.index_select(0, idx)
+        Un = None
+        if U is not None:
+            iu = torch.arange(ns, device=U.device) + adv
+            ou = iu > ns - 1
+            iu = torch.where(ou, iu - self.cycle_len * torch.div(iu - ns + self.cycle_len, self.cycle_len, rounding_mode="floor"), iu)
+            Un = U.index_select(0, iu)
+        return Xn[0].clone(), Xn, Un
+
+    def evaluate(self, X, U=None, params=None, want=("x", "u")):
+        """Continuity defects and Jacobian blocks of every scenario's current horizon (``FesShooting.evaluate``)."""
+        return self.shooting.evaluate(X, U, params, want=want)
+
+
+class OdeSolverLike:
+    """(scheme, n_integration_steps) pair accepted by ``scheme_and_steps``."""
+
+    def __init__(self, scheme, n_integration_steps):
+        self.scheme, self.n_integration_steps = scheme, n_integration_steps

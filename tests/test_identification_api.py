@@ -116,3 +116,29 @@ def test_data_extraction_and_input_checks(tmp_path):
         cf.DingModelFrequencyForceParameterIdentification(**{**kw, "data_path": ["x.csv"]})
     with pytest.raises(TypeError):
         cf.DingModelFrequencyForceParameterIdentification(**{**kw, "additional_key_settings": {"a_rest": {"initial_guess": "1"}}})
+
+
+def test_pickle_formats_round_trip(tmp_path):
+    """identification pickles and the SolutionToPickle dictionary (result/pickle.py:25-36)."""
+    from cocofest_b200 import pickle_io as pio
+
+    t = np.linspace(0, 1, 11)
+    for i in range(3):
+        pio.save_identification_data(str(tmp_path / f"s{i}.pkl"), t, (i + 1) * t, [0.0, 0.5], pulse_width=[3e-4, 4e-4])
+    d = pio.load_identification_data(str(tmp_path / "s1.pkl"))
+    assert set(d) == {"time", "force", "stim_time", "pulse_width"}
+    target, stim = pio.batch_targets([str(tmp_path / f"s{i}.pkl") for i in range(3)], 4, 1.0)
+    assert target.shape == (5, 3) and stim == [0.0, 0.5]
+    np.testing.assert_allclose(target[:, 2], 3 * np.linspace(0, 1, 5))
+    with open(tmp_path / "bad.pkl", "wb") as f:
+        pickle.dump({"time": [0]}, f)
+    with pytest.raises(KeyError):
+        pio.load_identification_data(str(tmp_path / "bad.pkl"))
+    sol = {"time": np.array([0.0, 0.1, 0.1, 0.2]), "states": {"F": np.array([[0.0, 1.0, 1.0, 2.0]]), "Cn": np.array([0.0, 0.5, 0.5, 0.7])},
+           "parameters": {"a_rest": 3009.0}, "parameters_bounds": {"a_rest": (1, 10000)}, "time_to_optimize": 0.01}
+    pio.SolutionToPickle(sol, "sol.pkl", str(tmp_path) + "/").pickle()
+    with open(tmp_path / "sol.pkl", "rb") as f:
+        out = pickle.load(f)
+    assert list(out) == ["time", "states", "control", "parameters", "parameters_bounds", "time_to_optimize", "bio_model_path"]
+    np.testing.assert_array_equal(out["time"], [0.0, 0.1, 0.2])
+    np.testing.assert_array_equal(out["states"]["F"], [0.0, 1.0, 2.0])
