@@ -126,6 +126,15 @@ def cpu_reference_rate(proto, n_traj, n_intervals, threads, repeat=1):
     return n_traj * n_intervals * 10 / best, best
 
 
+def host_threads():
+    """Host cores this process may use.  torchrun exports OMP_NUM_THREADS=1, which would silently turn the CPU arm
+    into a single-thread run: the oracle is told the thread count explicitly instead."""
+    try:
+        return len(os.sched_getaffinity(0))
+    except AttributeError:
+        return os.cpu_count() or 1
+
+
 def size_cpu_sample(proto, threads, target_s):
     """Picks (trajectories, intervals) of the same workload worth about target_s seconds of CPU work."""
     n0, k0 = 2 * max(threads, 1), min(proto["ns"], 132)
@@ -145,7 +154,7 @@ def run_reference(args):
     from oracle import fes_oracle_c as foc
 
     proto = protocols.fatigue_protocol(final_time=args.final_time)
-    threads = foc.max_threads()
+    threads = host_threads()
     n_traj, n_int = size_cpu_sample(proto, threads, target_s=8.0)
     for _ in range(args.warmup):
         cpu_reference_rate(proto, max(threads, n_traj // 8), n_int, threads)
@@ -337,7 +346,7 @@ def main():
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
         from oracle import fes_oracle_c as foc
 
-        threads = foc.max_threads()
+        threads = host_threads()
         n_traj, n_int = size_cpu_sample(proto, threads, target_s=12.0)
         rate, secs = cpu_reference_rate(proto, n_traj, n_int, threads)
         cpu = {"value": rate, "unit": UNIT, "cores": threads, "kind": "port", "seconds": secs,

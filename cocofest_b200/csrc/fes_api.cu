@@ -273,19 +273,45 @@ int ident_host_impl(const FesDesc *d, const FesIdentBuffers *h, const FesIdentOp
 }
 
 // ---- FMA peak probe ------------------------------------------------------------------------------
-template <typename T>
-__global__ void __launch_bounds__(256) fes_fma_probe_kernel(T *out, int iters, T m, T c) {
-    T acc[16];
+// Register-only dependent FMA chains; several (chains per thread, unroll, block size) shapes are timed and the
+// best rate is reported, so that the roofline denominator is the pipe's rate and not one loop's overhead.
+template <typename T, int CHAINS, int UNROLL>
+__global__ void fes_fma_probe_kernel(T *out, int iters, T m, T c) {
+    T acc[CHAINS];
 #pragma unroll
-    for (int j = 0; j < 16; ++j) acc[j] = (T)(threadIdx.x + j) * (T)1e-3;
-    for (int it = 0; it < iters; ++it) {
+    for (int j = 0; j < CHAINS; ++j) acc[j] = (T)(threadIdx.x + j) * (T)1e-3;
+    for (int it = 0; it < iters; it += UNROLL) {
 #pragma unroll
-        for (int j = 0; j < 16; ++j) acc[j] = xfma(acc[j], m, c);
+        for (int u = 0; u < UNROLL; ++u) {
+#pragma unroll
+            for (int j = 0; j < CHAINS; ++j) acc[j] = xfma(acc[j], m, c);
+        }
     }
     T sum = 0;
 #pragma unroll
-    for (int j = 0; j < 16; ++j) sum += acc[j];
-    if (sum == (T)123456789) out[0] = sum;  // keeps the chain alive, practically never taken
+    for (int j = 0; j < CHAINS; ++j) sum += acc[j];
+    if (sum == (T)123456789) out[0] = sum;  // keeps the chains alive, practically never taken
+}
+
+template <typename T, int CHAINS, int UNROLL>
+int probe_shape(int launches, int threads, int blocks_per_sm, int sms, T *out, cudaEvent_t e0, cudaEvent_t e1,
+                cudaStream_t s, double *best) {
+    const int iters = (sizeof(T) == 8 ? 65536 : 131072) / CHAINS;
+    const unsigned grid = (unsigned)(sms * blocks_per_sm);
+    int rc = 0;
+    for (int l = 0; l < launches + 1; ++l) {
+        cudaEventRecord(e0, s);
+        fes_fma_probe_kernel<T, CHAINS, UNROLL><<<grid, threads, 0, s>>>(out, iters, (T)0.999999, (T)1e-7);
+        cudaEventRecord(e1, s);
+        rc = (int)cudaEventSynchronize(e1);
+        ++g_launches;
+        if (rc) return rc;
+        float ms = 0.f;
+        cudaEventElapsedTime(&ms, e0, e1);
+        const double flops = 2.0 * CHAINS * (double)iters * (double)threads * (double)grid;
+        if (l > 0 && ms > 0.f) *best = std::max(*best, flops / (ms * 1e-3) / 1e12);
+    }
+    return (int)cudaGetLastError();
 }
 
 template <typename T>
@@ -299,25 +325,15 @@ int probe_impl(int launches, cudaStream_t s, double *tflops) {
     cudaEvent_t e0, e1;
     cudaEventCreate(&e0);
     cudaEventCreate(&e1);
-    const int iters = sizeof(T) == 8 ? 4096 : 8192;
-    const unsigned grid = (unsigned)sms * 8;
     double best = 0.0;
-    for (int l = 0; l < launches + 1; ++l) {
-        cudaEventRecord(e0, s);
-        fes_fma_probe_kernel<T><<<grid, 256, 0, s>>>(out, iters, (T)0.999999, (T)1e-7);
-        cudaEventRecord(e1, s);
-        rc = (int)cudaEventSynchronize(e1);
-        ++g_launches;
-        if (rc) break;
-        float ms = 0.f;
-        cudaEventElapsedTime(&ms, e0, e1);
-        const double flops = 2.0 * 16.0 * (double)iters * 256.0 * (double)grid;
-        if (l > 0 && ms > 0.f) best = std::max(best, flops / (ms * 1e-3) / 1e12);
-    }
+    rc = probe_shape<T, 16, 1>(launches, 256, 8, sms, out, e0, e1, s, &best);
+    if (!rc) rc = probe_shape<T, 16, 8>(launches, 256, 8, sms, out, e0, e1, s, &best);
+    if (!rc) rc = probe_shape<T, 8, 16>(launches, 128, 16, sms, out, e0, e1, s, &best);
+    if (!rc) rc = probe_shape<T, 32, 4>(launches, 128, 8, sms, out, e0, e1, s, &best);
+    if (!rc) rc = probe_shape<T, 8, 16>(launches, 1024, 2, sms, out, e0, e1, s, &best);
     cudaEventDestroy(e0);
     cudaEventDestroy(e1);
     cudaFree(out);
-    if (rc == 0) rc = (int)cudaGetLastError();
     *tflops = best;
     return rc;
 }
