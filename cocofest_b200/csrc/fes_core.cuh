@@ -476,6 +476,26 @@ FES_HD void rk_step_scheme(const Traj<T> &tr, const Interval<T, Dirs<KIND, FAT, 
     const double zf = (double)tr.kappa * (double)h, zc = (double)tr.inv_tauc * (double)h;
     double mus = tg.mu, mun = tg.mu, nus = tg.nu, nun = tg.nu;
     const T Etc = iv.E * tr.inv_tauc;  // Cn' = (E eps - Cn)/tauc = Etc eps - Cn/tauc
+    // Nominal fatigue rows, reduced within the step exactly like the tangent ones: with the offsets d = x - rest at
+    // the step start,  A(stage) = A_rest + dA m_s + alpha_a Wn,  Wn' = F - Wn/tau_fat (Wn = 0 at the step start),
+    // m_s = the scheme's stage values of m' = -m/tau_fat from m = 1 (loop-invariant, hoisted by the compiler).
+    constexpr int NXN = FAT ? 2 : NX;  // nominal components advanced by the generic update below
+    T fm[NS + 1];                      // fm[s] = m at stage s, fm[NS] = m after the step
+    T dA = T(0), dT1 = T(0), dKm = T(0), wn_s = T(0), wn_n = T(0);
+    if constexpr (FAT) {
+        const T z = tr.kappa * h;
+        fm[0] = T(1);
+        T acc = T(1);
+        static_for<0, NS>([&](auto is) {
+            constexpr int s = decltype(is)::value;
+            if constexpr (TB::beta(s) != 0.0) acc = xfma(-z * T(TB::beta(s)), fm[s], acc);
+            if constexpr (s + 1 < NS) fm[s + 1] = xfma(-z * T(TB::alpha(s + 1)), fm[s], T(1));
+        });
+        fm[NS] = acc;
+        dA = x[2] - tr.a_rest;
+        dT1 = x[3] - tr.tau1_rest;
+        dKm = x[4] - tr.km_rest;
+    }
 
     static_for<0, NS>([&](auto is) {
         constexpr int s = decltype(is)::value;
@@ -487,8 +507,18 @@ FES_HD void rk_step_scheme(const Traj<T> &tr, const Interval<T, Dirs<KIND, FAT, 
         {
             T k[NX];
             nominal_rhs<T, KIND, FAT, NEED>(tr, Etc * eps, iv.g, xs, k, st);
+            if constexpr (FAT) {  // before xs[1] moves on: Wn' at this stage (k[2..4] of nominal_rhs are dead here)
+                const T kw = s == 0 ? xs[1] : xfma(-tr.kappa, wn_s, xs[1]);
+                if constexpr (TB::beta(s) != 0.0) wn_n = s == 0 ? hb * kw : xfma(hb, kw, wn_n);
+                if constexpr (!LAST) {
+                    wn_s = ha * kw;
+                    xs[2] = xfma(tr.alpha_a, wn_s, xfma(dA, fm[s + 1], tr.a_rest));
+                    xs[3] = xfma(tr.alpha_tau1, wn_s, xfma(dT1, fm[s + 1], tr.tau1_rest));
+                    xs[4] = xfma(tr.alpha_km, wn_s, xfma(dKm, fm[s + 1], tr.km_rest));
+                }
+            }
 #pragma unroll
-            for (int j = 0; j < NX; ++j) {
+            for (int j = 0; j < NXN; ++j) {
                 if constexpr (TB::beta(s) != 0.0) xn[j] = xfma(hb, k[j], xn[j]);
                 if constexpr (!LAST) xs[j] = xfma(ha, k[j], x[j]);
             }
@@ -524,7 +554,12 @@ FES_HD void rk_step_scheme(const Traj<T> &tr, const Interval<T, Dirs<KIND, FAT, 
         });
     });
 #pragma unroll
-    for (int j = 0; j < NX; ++j) x[j] = xn[j];
+    for (int j = 0; j < NXN; ++j) x[j] = xn[j];
+    if constexpr (FAT) {
+        x[2] = xfma(tr.alpha_a, wn_n, xfma(dA, fm[NS], tr.a_rest));
+        x[3] = xfma(tr.alpha_tau1, wn_n, xfma(dT1, fm[NS], tr.tau1_rest));
+        x[4] = xfma(tr.alpha_km, wn_n, xfma(dKm, fm[NS], tr.km_rest));
+    }
     static_for<0, ND>([&](auto ic) {
         constexpr int d = decltype(ic)::value;
         constexpr int C = D::code(d);

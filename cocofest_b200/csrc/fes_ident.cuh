@@ -48,12 +48,15 @@ struct IdentArgs {
 };
 
 // cost, gradient and Gauss-Newton matrix of one candidate (parameters pc[NP]) -------------------------
+// The np + np(np+1)/2 running sums live in `acc` (element i at acc[i * stride]): on the device that is a
+// conflict-free column of shared memory per thread (stride = block size), which keeps 88 registers (Hmed, fp64)
+// out of the RK loop; they are touched once per node, i.e. once per S RK steps.  pc[j * pstride] = parameter j.
 template <typename T, int KIND>
-FES_HD void ident_eval(const IdentArgs<T> &a, int64_t b, const T *pc, const T *eps, T &cost, T *g, T *H) {
+FES_HD void ident_eval(const IdentArgs<T> &a, int64_t b, const T *pc, int pstride, const T *eps, T &cost, T *acc, int stride) {
     using I = IdentDims<KIND>;
     constexpr int NPK = I::NPK;
     Traj<T> tr;
-    load_traj(tr, [&](int j) { return pc[j]; }, a.tauc, a.r0_km);
+    load_traj(tr, [&](int j) { return pc[j * pstride]; }, a.tauc, a.r0_km);
     T x[2] = {T(0), T(0)};
     if (a.x0 != nullptr) {
         x[0] = a.x0[b];
@@ -62,8 +65,8 @@ FES_HD void ident_eval(const IdentArgs<T> &a, int64_t b, const T *pc, const T *e
     Tangent<T, KIND, false, G_P> tg;
     tg.init();
     cost = T(0);
-    static_for<0, NPK>([&](auto ic) { g[decltype(ic)::value] = T(0); });
-    static_for<0, I::NH>([&](auto ic) { H[decltype(ic)::value] = T(0); });
+    T *g = acc, *H = acc + NPK * stride;
+    static_for<0, NPK + I::NH>([&](auto ic) { acc[decltype(ic)::value * stride] = T(0); });
     auto fold = [&](int node) {
         const T w = a.weight != nullptr ? a.weight[node] : a.dt;
         const T r = x[1] - a.target[(int64_t)node * a.gB + b * a.gS];
@@ -72,11 +75,11 @@ FES_HD void ident_eval(const IdentArgs<T> &a, int64_t b, const T *pc, const T *e
         static_for<0, NPK>([&](auto id) {
             constexpr int d = decltype(id)::value;
             const T vd = tg.V[d][1];
-            g[d] = xfma(wr + wr, vd, g[d]);
+            g[d * stride] = xfma(wr + wr, vd, g[d * stride]);
             const T wv = (w + w) * vd;
             static_for<d, NPK>([&](auto ie) {
                 constexpr int e = decltype(ie)::value;
-                H[I::hidx(d, e)] = xfma(wv, tg.V[e][1], H[I::hidx(d, e)]);
+                H[I::hidx(d, e) * stride] = xfma(wv, tg.V[e][1], H[I::hidx(d, e) * stride]);
             });
         });
     };
@@ -94,24 +97,30 @@ FES_HD void ident_eval(const IdentArgs<T> &a, int64_t b, const T *pc, const T *e
 }
 
 // Marquardt-scaled step: solves (H + lambda diag(H)) delta = -g on the free parameters (p_mask: identified and
-// not held on a bound) by an in-register Cholesky factorisation.  Returns false when the matrix is not
-// numerically positive definite.
-template <typename T, int KIND>
-FES_HD bool ident_solve(const T *g, const T *H, T lambda, int p_mask, T *delta) {
+// not held on a bound) by an in-register Cholesky factorisation.  gH(i) reads element i of the current
+// [gradient | Gauss-Newton upper triangle] record.  Returns false when the matrix is not numerically positive
+// definite.
+template <typename T, int KIND, class GH>
+FES_HD bool ident_solve(GH gH, T lambda, int p_mask, T *delta) {
     using I = IdentDims<KIND>;
     constexpr int NPK = I::NPK;
     T L[I::NH];
     T rhs[NPK];
+    int on_mask = 0;
     static_for<0, NPK>([&](auto id) {
         constexpr int d = decltype(id)::value;
-        const bool on = ((p_mask >> d) & 1) && H[I::hidx(d, d)] > T(0);
-        static_for<d, NPK>([&](auto ie) {
+        L[I::hidx(d, d)] = gH(NPK + I::hidx(d, d));
+        if (((p_mask >> d) & 1) && L[I::hidx(d, d)] > T(0)) on_mask |= 1 << d;
+    });
+    static_for<0, NPK>([&](auto id) {
+        constexpr int d = decltype(id)::value;
+        const bool on = (on_mask >> d) & 1;
+        static_for<d + 1, NPK>([&](auto ie) {
             constexpr int e = decltype(ie)::value;
-            const bool on_e = ((p_mask >> e) & 1) && H[I::hidx(e, e)] > T(0);
-            L[I::hidx(d, e)] = (on && on_e) ? H[I::hidx(d, e)] : T(0);
+            L[I::hidx(d, e)] = (on && ((on_mask >> e) & 1)) ? gH(NPK + I::hidx(d, e)) : T(0);
         });
-        L[I::hidx(d, d)] = on ? H[I::hidx(d, d)] * (T(1) + lambda) : T(1);
-        rhs[d] = on ? -g[d] : T(0);
+        L[I::hidx(d, d)] = on ? L[I::hidx(d, d)] * (T(1) + lambda) : T(1);
+        rhs[d] = on ? -gH(d) : T(0);
     });
     bool ok = true;
     // upper Cholesky H = U^T U, row by row
@@ -156,73 +165,83 @@ FES_HD bool ident_solve(const T *g, const T *H, T lambda, int p_mask, T *delta) 
 }
 
 // the whole identification of candidate b ------------------------------------------------------------------
+// Per-candidate scratch `acc` (element i at acc[i * stride]; a shared-memory column per thread on the device):
+//   [0, np)                gradient sums of the trial point      [np, np + nh)   Gauss-Newton sums of the trial point
+//   [np + nh, + 14)        trial parameters
+// The CURRENT point lives in the output arrays (params_out, cost, grad, hess), so that only the integration state
+// occupies registers inside the RK loop.
+template <int KIND>
+constexpr int ident_scratch() { return IdentDims<KIND>::NPK + IdentDims<KIND>::NH + NP; }
+
 template <typename T, int KIND>
-FES_HD void ident_candidate(const IdentArgs<T> &a, int64_t b, const T *eps) {
+FES_HD void ident_candidate(const IdentArgs<T> &a, int64_t b, const T *eps, T *acc, int stride) {
     using I = IdentDims<KIND>;
     constexpr int NPK = I::NPK;
     constexpr int NH = I::NH;
-    T pc[NP];
+    T *pt = acc + (NPK + NH) * stride;
+    auto cur_p = [&](int j) -> T & { return a.params_out[j * a.B + b]; };
 #pragma unroll
-    for (int j = 0; j < NP; ++j) pc[j] = a.params[j * a.pB + b * a.pS];
+    for (int j = 0; j < NP; ++j) pt[j * stride] = a.params[j * a.pB + b * a.pS];
     if (a.max_iter > 0) {  // the iteration starts inside the box
         static_for<0, NPK>([&](auto id) {
             constexpr int d = decltype(id)::value;
             constexpr int j = I::canon(d);
             if (!((a.p_mask >> d) & 1)) return;
-            if (a.lower != nullptr && pc[j] < a.lower[j]) pc[j] = a.lower[j];
-            if (a.upper != nullptr && pc[j] > a.upper[j]) pc[j] = a.upper[j];
+            T v = pt[j * stride];
+            if (a.lower != nullptr && v < a.lower[j]) v = a.lower[j];
+            if (a.upper != nullptr && v > a.upper[j]) v = a.upper[j];
+            pt[j * stride] = v;
         });
     }
-    T cost, g[NPK], H[NH];
-    ident_eval<T, KIND>(a, b, pc, eps, cost, g, H);
-    auto publish = [&]() {
+    T cost;
+    ident_eval<T, KIND>(a, b, pt, stride, eps, cost, acc, stride);
+    auto publish = [&]() {  // the trial point becomes the current one
         a.cost[b] = cost;
-        static_for<0, NPK>([&](auto ic) { a.grad[decltype(ic)::value * a.B + b] = g[decltype(ic)::value]; });
-        static_for<0, NH>([&](auto ic) { a.hess[decltype(ic)::value * a.B + b] = H[decltype(ic)::value]; });
+        static_for<0, NPK + NH>([&](auto ic) {
+            constexpr int i = decltype(ic)::value;
+            (i < NPK ? a.grad[i * a.B + b] : a.hess[(i - NPK) * a.B + b]) = acc[i * stride];
+        });
+#pragma unroll
+        for (int j = 0; j < NP; ++j) cur_p(j) = pt[j * stride];
     };
     publish();
     T cur = cost;
     T lambda = a.lambda0;
     int evals = 1;
+    auto gH = [&](int i) { return i < NPK ? a.grad[i * a.B + b] : a.hess[(i - NPK) * a.B + b]; };
     for (int it = 0; it < a.max_iter; ++it) {
         if (!(cur > T(0)) || !(lambda < T(1e15))) break;  // exact fit, NaN start, or no acceptable step left
-        // current gradient / Gauss-Newton matrix live in the output arrays (registers hold the trial ones)
-        static_for<0, NPK>([&](auto ic) { g[decltype(ic)::value] = a.grad[decltype(ic)::value * a.B + b]; });
-        static_for<0, NH>([&](auto ic) { H[decltype(ic)::value] = a.hess[decltype(ic)::value * a.B + b]; });
         // active set: a parameter sitting on a bound whose gradient pushes it further out is held for this step
         int free_mask = a.p_mask;
         static_for<0, NPK>([&](auto id) {
             constexpr int d = decltype(id)::value;
             constexpr int j = I::canon(d);
-            if (a.lower != nullptr && pc[j] <= a.lower[j] && g[d] > T(0)) free_mask &= ~(1 << d);
-            if (a.upper != nullptr && pc[j] >= a.upper[j] && g[d] < T(0)) free_mask &= ~(1 << d);
+            const T gd = gH(d), pj = cur_p(j);
+            if (a.lower != nullptr && pj <= a.lower[j] && gd > T(0)) free_mask &= ~(1 << d);
+            if (a.upper != nullptr && pj >= a.upper[j] && gd < T(0)) free_mask &= ~(1 << d);
         });
         T delta[NPK];
-        if (!ident_solve<T, KIND>(g, H, lambda, free_mask, delta)) {
+        if (!ident_solve<T, KIND>(gH, lambda, free_mask, delta)) {
             lambda *= T(10);
             continue;
         }
-        T pt[NP];
-#pragma unroll
-        for (int j = 0; j < NP; ++j) pt[j] = pc[j];
         T step = T(0);
         static_for<0, NPK>([&](auto id) {
             constexpr int d = decltype(id)::value;
             constexpr int j = I::canon(d);
-            T v = pc[j] + delta[d];
+            const T pj = cur_p(j);
+            T v = pj + delta[d];
             if (a.lower != nullptr) v = v < a.lower[j] ? a.lower[j] : v;
             if (a.upper != nullptr) v = v > a.upper[j] ? a.upper[j] : v;
-            const T rel = xabs(v - pc[j]) / (xabs(pc[j]) + T(1e-30));
+            const T rel = xabs(v - pj) / (xabs(pj) + T(1e-30));
             step = rel > step ? rel : step;
-            pt[j] = v;
+            pt[j * stride] = v;  // rows that are not P-columns keep the current (= starting) value
         });
         if (!(step > T(0))) break;  // pinned on the box in every identified direction
-        ident_eval<T, KIND>(a, b, pt, eps, cost, g, H);
+        ident_eval<T, KIND>(a, b, pt, stride, eps, cost, acc, stride);
         ++evals;
         if (cost < cur) {
             const T gain = cur - cost;
-#pragma unroll
-            for (int j = 0; j < NP; ++j) pc[j] = pt[j];
             publish();
             const bool done = gain <= a.ftol * cur || step <= a.xtol;
             cur = cost;
@@ -233,28 +252,30 @@ FES_HD void ident_candidate(const IdentArgs<T> &a, int64_t b, const T *eps) {
             lambda *= T(4);
         }
     }
-#pragma unroll
-    for (int j = 0; j < NP; ++j) a.params_out[j * a.B + b] = pc[j];
     if (a.iters != nullptr) a.iters[b] = evals;
 }
 
 #if defined(__CUDACC__)
 
+#ifndef FES_IDENT_MIN_BLOCKS  // sweep knob (scripts/build_variants.sh)
+#define FES_IDENT_MIN_BLOCKS 2
+#endif
 template <typename T, int KIND>
-__global__ void __launch_bounds__(BLOCK, 2) fes_ident_kernel(const IdentArgs<T> a) {
+__global__ void __launch_bounds__(BLOCK, FES_IDENT_MIN_BLOCKS) fes_ident_kernel(const IdentArgs<T> a) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     T *s_eps = reinterpret_cast<T *>(smem_raw);
+    T *s_acc = s_eps + ((2 * a.S + 1 + 3) & ~3);  // [ident_scratch][BLOCK]
     for (int i = threadIdx.x; i < 2 * a.S + 1; i += BLOCK) s_eps[i] = a.eps[i];
     __syncthreads();
     const int64_t b = (int64_t)blockIdx.x * BLOCK + threadIdx.x;
     if (b >= a.B) return;
-    ident_candidate<T, KIND>(a, b, s_eps);
+    ident_candidate<T, KIND>(a, b, s_eps, s_acc + threadIdx.x, BLOCK);
 }
 
 template <typename T, int KIND>
 int launch_ident_k(const IdentArgs<T> &a, cudaStream_t s) {
     const unsigned grid = (unsigned)((a.B + BLOCK - 1) / BLOCK);
-    const size_t smem = ((2 * a.S + 1 + 3) & ~3) * sizeof(T);
+    const size_t smem = (((2 * a.S + 1 + 3) & ~3) + (size_t)ident_scratch<KIND>() * BLOCK) * sizeof(T);
     fes_ident_kernel<T, KIND><<<grid, BLOCK, smem, s>>>(a);
     return (int)cudaGetLastError();
 }

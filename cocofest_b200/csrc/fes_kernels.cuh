@@ -37,8 +37,10 @@ constexpr int min_blocks() {
 #ifdef FES_MIN_BLOCKS
     return FES_MIN_BLOCKS;
 #else
+    // same effect on the two-state kernels (Hmed P columns: 182 registers unconstrained, +16 % under the 204 cap,
+    // profiles/r01_tune_ident_g.txt); the dense fatigue parameter columns (P, P|PF: 204-254 registers) stay free
     constexpr bool red = FAT && (GROUPS == G_X0 || GROUPS == G_U || GROUPS == G_W || (GROUPS == (G_X0 | G_U) && KIND == DING2007));
-    return (sizeof(T) == 8 && red) ? 5 : 2;
+    return (sizeof(T) == 8 && (red || !FAT)) ? 5 : 2;
 #endif
 }
 #define FES_LAUNCH_BOUNDS __launch_bounds__(BLOCK, (min_blocks<T, KIND, FAT, GROUPS>()))

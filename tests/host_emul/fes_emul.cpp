@@ -222,11 +222,12 @@ int ident_impl(const FesDesc *d, const FesIdentBuffers *b, const FesIdentOptions
     }
     IdentArgs<T> a;
     fill_ident_args<T>(d, b, o, c, a);
+    T acc[8 + 36 + FES_NP];  // per-candidate scratch (ident_scratch<KIND>(), shared memory on the device)
     for (int64_t i = 0; i < a.B; ++i) {
         switch (d->model_kind) {
-            case 0: ident_candidate<T, 0>(a, i, a.eps); break;
-            case 1: ident_candidate<T, 1>(a, i, a.eps); break;
-            default: ident_candidate<T, 2>(a, i, a.eps); break;
+            case 0: ident_candidate<T, 0>(a, i, a.eps, acc, 1); break;
+            case 1: ident_candidate<T, 1>(a, i, a.eps, acc, 1); break;
+            default: ident_candidate<T, 2>(a, i, a.eps, acc, 1); break;
         }
     }
     return 0;
