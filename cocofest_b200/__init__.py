@@ -19,7 +19,8 @@ from .models import (
 )
 from .ode_solver import OdeSolver
 from .ivp_fes import IvpFes
-from .ocp_fes import OcpFes, FesShooting
+from .ocp_fes import OcpFes, FesShooting, FesNmpcBatch
+from .bioptim_seam import FesIntegrator
 from .identification import (
     DingModelFrequencyForceParameterIdentification,
     DingModelPulseIntensityFrequencyForceParameterIdentification,
@@ -27,7 +28,7 @@ from .identification import (
 )
 
 __all__ = [
-    "fes", "FesModel", "ModelMaker", "OdeSolver", "IvpFes", "OcpFes", "FesShooting",
+    "fes", "FesModel", "ModelMaker", "OdeSolver", "IvpFes", "OcpFes", "FesShooting", "FesNmpcBatch", "FesIntegrator",
     "DingModelFrequency", "DingModelFrequencyWithFatigue",
     "DingModelPulseWidthFrequency", "DingModelPulseWidthFrequencyWithFatigue",
     "DingModelPulseIntensityFrequency", "DingModelPulseIntensityFrequencyWithFatigue",
