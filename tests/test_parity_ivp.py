@@ -185,3 +185,45 @@ def test_ivp_argument_errors(backend):
         fes.ivp(pb["kind"], pb["fat"], params, x0, win, pb["dt"], ctrl=ctrl, n_shooting=pb["ns"], scheme=3)
     with pytest.raises(FesLibraryError):
         fes.ivp(pb["kind"], pb["fat"], params, x0, win, pb["dt"], ctrl=ctrl, n_shooting=pb["ns"], n_steps=1000)
+
+
+@pytest.mark.parametrize("backend", BACKENDS, indirect=True)
+@pytest.mark.parametrize("name", ["ding2003_with_fatigue", "hmed2018"])
+@pytest.mark.parametrize("B", [1, 130])
+def test_ivp_edge_sizes(backend, name, B):
+    """Limits of the ABI: truncation window of 64 pulses (FesDesc.n_trunc max), 256 sub-steps per interval
+    (n_steps max), a single trajectory and a batch that fills two blocks and two lanes of a third."""
+    pb = random_problem(name, B=B, N=64, ns=3, freq=50.0, seed=8, shared_ctrl=(B == 1))
+    params, x0, win, ctrl = to_lib(pb, backend)
+    S = 256
+    res = fes.ivp(pb["kind"], pb["fat"], params, x0, win, pb["dt"], n_steps=S, ctrl=ctrl, n_shooting=pb["ns"],
+                  dirs=fes.FES_DIR_X0, trace="nodes")
+    ref = foc.ivp(pb["kind"], pb["fat"], 4, pb["N"], pb["ns"], S, pb["dt"], pb["tauc"], fo.R0_KM_RELATIONSHIP,
+                  pb["params"], pb["x0"], oracle_win(pb), pb["u"], seed_x0=True)
+    assert rel_err(res.x_final.cpu().numpy().T, ref["final"]) < RTOL64
+    gs = np.transpose(res.sens_final.cpu().numpy(), (2, 0, 1))
+    assert np.max(np.abs(gs - ref["sens_final"])) < RTOL64 * np.max(np.abs(ref["sens_final"]))
+    assert res.trace.shape == (pb["ns"] + 1, pb["nx"], B)
+    from cocofest_b200._lib import FesLibraryError
+    with pytest.raises(FesLibraryError):  # one past the limits
+        fes.ivp(pb["kind"], pb["fat"], params, x0, win, pb["dt"], n_steps=257, ctrl=ctrl, n_shooting=pb["ns"])
+
+
+@pytest.mark.parametrize("backend", BACKENDS, indirect=True)
+def test_ivp_window_of_pads_only_is_pure_decay(backend):
+    """Before the first pulse the window holds only the -10 000 000 pads (ding2003.py:394-397): every exp
+    underflows to 0, Cn decays as exp(-t/tauc) under RK4 and F relaxes -- no NaN, same numbers as the oracle."""
+    kind, fat = MODELS["ding2003_with_fatigue"]
+    ns, dt, N, S = 4, 0.05, 5, 10
+    win = np.full((ns + 1, N), float(fes.PAD_TIME))
+    p = fo.default_params(kind)
+    x0 = np.array([[0.5, 80.0, 2800.0, 0.055, 0.12]])
+    res = fes.ivp(kind, fat, torch.tensor(p, device=backend), torch.tensor(x0.T.copy(), device=backend),
+                  torch.tensor(win, device=backend), dt, n_steps=S, n_shooting=ns, trace="nodes")
+    ref = foc.ivp(kind, fat, 4, N, ns, S, dt, fo.default_tauc(kind), fo.R0_KM_RELATIONSHIP, p[None], x0, win[None])
+    got = res.x_final.cpu().numpy().T
+    assert np.all(np.isfinite(got)) and rel_err(got, ref["final"]) < RTOL64
+    # Cn obeys the linear test equation: one RK4 step multiplies it by the degree-4 Taylor polynomial of exp(-h/tauc)
+    z = -(dt / S) / fo.default_tauc(kind)
+    amp = (1 + z + z * z / 2 + z ** 3 / 6 + z ** 4 / 24) ** (ns * S)
+    assert abs(got[0, 0] / (0.5 * amp) - 1) < 1e-12
