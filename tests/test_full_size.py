@@ -107,8 +107,8 @@ def test_config4_full_identification_costs_and_monotone_lm():
     ok = torch.isfinite(ev.cost)
     assert bool((lm.cost[ok] <= ev.cost[ok]).all())
     assert float(lm.cost[ok].median()) < 1e-3 * float(ev.cost[ok].median())
-    lo_v = torch.tensor([lo.get(n, -np.inf) for n in fes.PARAM_NAMES], device=dev)[:, None]
-    hi_v = torch.tensor([hi.get(n, np.inf) for n in fes.PARAM_NAMES], device=dev)[:, None]
+    lo_v = torch.tensor([lo.get(n, -np.inf) for n in fes.PARAM_NAMES], dtype=torch.float64, device=dev)[:, None]
+    hi_v = torch.tensor([hi.get(n, np.inf) for n in fes.PARAM_NAMES], dtype=torch.float64, device=dev)[:, None]
     assert bool(((lm.params >= lo_v) & (lm.params <= hi_v)).all())
     # re-evaluating the returned points reproduces the returned costs bit for bit
     again = fes.identify(fes.FES_HMED2018, lm.params, win, dt, tgt, ctrl=ctrl, max_iter=0)
