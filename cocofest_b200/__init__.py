@@ -21,6 +21,7 @@ from .ode_solver import OdeSolver
 from .ivp_fes import IvpFes
 from .ocp_fes import OcpFes, FesShooting, FesNmpcBatch
 from .bioptim_seam import FesIntegrator
+from .fourier_approx import FourierSeries
 from .identification import (
     DingModelFrequencyForceParameterIdentification,
     DingModelPulseIntensityFrequencyForceParameterIdentification,
@@ -28,7 +29,7 @@ from .identification import (
 )
 
 __all__ = [
-    "fes", "FesModel", "ModelMaker", "OdeSolver", "IvpFes", "OcpFes", "FesShooting", "FesNmpcBatch", "FesIntegrator",
+    "fes", "FesModel", "ModelMaker", "OdeSolver", "IvpFes", "OcpFes", "FesShooting", "FesNmpcBatch", "FesIntegrator", "FourierSeries",
     "DingModelFrequency", "DingModelFrequencyWithFatigue",
     "DingModelPulseWidthFrequency", "DingModelPulseWidthFrequencyWithFatigue",
     "DingModelPulseIntensityFrequency", "DingModelPulseIntensityFrequencyWithFatigue",
