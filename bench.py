@@ -183,7 +183,8 @@ def run_reference(args):
 
 def workload_config(args, proto):
     return {
-        "workload": "BASELINE configs[1]: Ding2003+fatigue, 33 Hz 1s-on/1s-off protocol, fp64, d x(T)/d x0 sensitivities",
+        "workload": "BASELINE configs[1]: Ding2003+fatigue, 33 Hz 1s-on/1s-off protocol, "
+                    + ("fp32 mode" if getattr(args, "dtype", "f64") == "f32" else "fp64") + ", d x(T)/d x0 sensitivities",
         "model": "DingModelFrequencyWithFatigue", "batch_per_gpu": args.batch, "final_time_s": args.final_time,
         "n_shooting": proto["ns"], "n_integration_steps": 10, "sum_stim_truncation": proto["N"], "scheme": "RK4",
         "sensitivity_columns": 5, "trace": "all 5 states at every node for the first 1024 trajectories",
@@ -203,6 +204,8 @@ def main():
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--dtype", default="f64", choices=["f64", "f32"],
+                    help="arithmetic type of the path (f32 = north_star's 1e-4 mode, reported against the FFMA rate)")
     args = ap.parse_args()
     if args.warmup < 3:
         args.warmup = 3
@@ -230,8 +233,10 @@ def main():
     B, ns, S = args.batch, proto["ns"], 10
     trace_B = min(1024, B)
     # host-resident inputs (pinned) for the end-to-end arm; device-resident copies for the kernel arm
+    f32 = args.dtype == "f32"
+    tdt, esz = (torch.float32, 4) if f32 else (torch.float64, 8)
     params_h, x0_h = protocols.fatigue_population(B, offset=rank)
-    params_h, x0_h = params_h.pin_memory(), x0_h.pin_memory()
+    params_h, x0_h = params_h.to(tdt).pin_memory(), x0_h.to(tdt).pin_memory()
     win_h = torch.tensor(proto["win"]).pin_memory()
     params_d, x0_d, win_d = params_h.to(dev), x0_h.to(dev), win_h.to(dev)
     flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)
@@ -254,7 +259,7 @@ def main():
     for _ in range(args.warmup):
         device_step()
         flush.fill_(1)
-    fp64_peak = fes.probe_fma_peak(False, launches=5, device=dev)
+    fp64_peak = fes.probe_fma_peak(f32, launches=5, device=dev)  # FFMA rate in f32 mode
 
     # ---- kernel arm: inputs resident in HBM ----------------------------------------------------------------
     sampler = ClockSampler(physical_gpu_index(local))
@@ -302,11 +307,11 @@ def main():
         t = torch.tensor([el], dtype=torch.float64, device=dev)
         if world > 1:
             dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        h2d = params_h.numel() * 8 + x0_h.numel() * 8 + ns * proto["N"] * 8
-        d2h = r.x_final.numel() * 8 + r.sens_final.numel() * 8 + r.trace.numel() * 8
+        h2d = params_h.numel() * esz + x0_h.numel() * esz + ns * proto["N"] * 8
+        d2h = (r.x_final.numel() + r.sens_final.numel() + r.trace.numel()) * esz
         e2e = {"value": world * units_per_step * args.steps / float(t.item()), "unit": UNIT,
                "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
-               "api": "cocofest_b200.fes.ivp on pinned host tensors -> fes_ivp_host_f64 (C ABI)"}
+               "api": f"cocofest_b200.fes.ivp on pinned host tensors -> fes_ivp_host_{args.dtype} (C ABI)"}
 
     # ---- roofline of the dominant kernel (fes_ivp_kernel<double, ding2003, fatigue, X0>) -----------------
     flop = flop_alg_per_step()
@@ -317,21 +322,21 @@ def main():
         static = json.loads((ROOT / "profiles" / "r01_ivp_x0_static.json").read_text())
     except Exception:
         pass
-    inst = static.get("fp64_inst_per_rk4_step")
+    inst = None if f32 else static.get("fp64_inst_per_rk4_step")  # the SASS count is of the fp64 kernel
     traffic = None
     cap = static.get("ncu_full_capture", {})
-    if cap.get("batch") == B and cap.get("final_time_s") == args.final_time:
+    if not f32 and cap.get("batch") == B and cap.get("final_time_s") == args.final_time:
         traffic = cap.get("dram_bytes")
-    hbm_bytes = (params_d.numel() + 2 * x0_d.numel() + 25 * B + (ns + 1) * 5 * trace_B) * 8
+    hbm_bytes = (params_d.numel() + 2 * x0_d.numel() + 25 * B + (ns + 1) * 5 * trace_B) * esz
     peaks = {}
     try:
         peaks = json.loads((ROOT / "MEASURED_PEAKS.json").read_text())
     except Exception:
         pass
     roofline = {
-        "bound": "fp64", "achieved": achieved, "peak": fp64_peak, "unit": "TFLOP/s", "frac": achieved / fp64_peak if fp64_peak else None,
+        "bound": "fp32" if f32 else "fp64", "achieved": achieved, "peak": fp64_peak, "unit": "TFLOP/s", "frac": achieved / fp64_peak if fp64_peak else None,
         "traffic": traffic,
-        "kernel": "fes_ivp_kernel<double, DING2003, fatigue, X0>", "kernel_ms": statistics.mean(kern_ms),
+        "kernel": f"fes_ivp_kernel<{'float' if f32 else 'double'}, DING2003, fatigue, X0>", "kernel_ms": statistics.mean(kern_ms),
         "flop_alg_per_trajectory_step": flop,
         "survey_dense_formulation": {"flop_per_trajectory_step": flop_survey_per_step(5, 5),
                                      "equivalent_tflops": flop_survey_per_step(5, 5) * units_per_step / kernel_s / 1e12,
@@ -341,7 +346,8 @@ def main():
             "inst_per_trajectory_step": inst, "issue_rate_ginst_s": inst * units_per_step / kernel_s / 1e9,
             "peak_ginst_s": fp64_peak * 1e3 / 2, "frac": inst * units_per_step / kernel_s / 1e9 / (fp64_peak * 1e3 / 2),
             "note": "DFMA+DMUL+DADD of the RK4 path counted in the shipped SASS; every one occupies a DFMA issue slot"},
-        "peak_source": "DFMA probe (fes_probe_fma_peak) measured in this run on this GPU; MEASURED_PEAKS.json holds no fp64 figure",
+        "peak_source": ("FFMA" if f32 else "DFMA") + " probe (fes_probe_fma_peak) measured in this run on this GPU; "
+                       "MEASURED_PEAKS.json holds no fp64 / fp32 figure",
         "hbm": {"algorithmic_bytes": hbm_bytes, "achieved_gbs": hbm_bytes / kernel_s / 1e9, "peak_gbs": peaks.get("hbm_gbs"),
                 "note": "state, parameters and tangents stay in registers: HBM is idle by design"},
     }
@@ -362,7 +368,7 @@ def main():
         line = {
             "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
             "ms_per_step": elapsed_ms / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
-            "dtype": "f64", "data": "synthetic", "config": workload_config(args, proto), "clocks": clocks,
+            "dtype": args.dtype, "data": "synthetic", "config": workload_config(args, proto), "clocks": clocks,
             "e2e": e2e, "gpu_launches": int(launches), "roofline": roofline, "cpu_baseline": cpu,
             "final_force_mean": float(res.x_final[1].mean().item()),
         }

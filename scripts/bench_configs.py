@@ -66,6 +66,7 @@ def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--configs", default="1,3,4,5")
     ap.add_argument("--scale", type=float, default=1.0)
+    ap.add_argument("--t2", type=int, default=300, help="protocol length of config 2 in seconds")
     ap.add_argument("--steps", type=int, default=3)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--dtype", default="f64", choices=["f64", "f32"])
@@ -97,6 +98,26 @@ def main():
                               B * ns * S, ms, 5, 0, out.trace.numel() * esz + out.x_final.numel() * esz, x0.numel() * esz,
                               peak, args.dtype, {"batch": B, "n_shooting": ns, "F_end": float(out.x_final[1, 0])})), flush=True)
         del out, x0
+
+    if 2 in wanted:
+        # BASELINE configs[1] as stated: forward only (no sensitivities), F at every node for the first 1024
+        # trajectories, final state for all; --t2 shortens the protocol for sweeps
+        B = 1 << 20
+        T = max(2, args.t2)
+        proto = protocols.fatigue_protocol(final_time=T)
+        p, x0 = protocols.fatigue_population(B, device=dev)
+        p, x0 = p.to(dt_t), x0.to(dt_t)
+        win = torch.tensor(proto["win"], device=dev)
+        ns = proto["ns"]
+        fn = lambda: fes.ivp(fes.FES_DING2003, True, p, x0, win, proto["dt"], n_steps=S, n_shooting=ns, trace="nodes",
+                             trace_batch=1024, dtype=dt_t)
+        out, ms = timed(fn, args.steps, args.warmup, flush)
+        print(json.dumps(line(f"2: Ding2003+fatigue 33 Hz protocol, {T} s, forward only (no sensitivities), 1M trajectories",
+                              B * ns * S, ms, 5, 0, (out.trace.numel() + out.x_final.numel()) * esz,
+                              (p.numel() + x0.numel()) * esz, peak, args.dtype,
+                              {"batch": B, "n_shooting": ns, "final_time_s": T, "F_end_mean": float(out.x_final[1].mean())})),
+              flush=True)
+        del out, p, x0
 
     if 3 in wanted:
         B = max(1024, int((1 << 22) * args.scale))
