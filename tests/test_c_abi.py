@@ -1,0 +1,47 @@
+"""The drop-in boundary used from plain C (tests/c_abi/abi_client.c): libfes_b200.so is self-contained (no torch,
+no Python), refuses bad arguments with negative codes, fails loudly without a device, and on a B200 reproduces the
+reference's own golden force trajectory (tests/shard1/test_ivp.py:28-44) through fes_ivp_host_f64."""
+import json
+import subprocess
+from pathlib import Path
+
+import numpy as np
+import pytest
+import torch
+
+from tests.conftest import ROOT
+
+SRC = ROOT / "tests" / "c_abi" / "abi_client.c"
+EXE = ROOT / "tests" / "c_abi" / "abi_client"
+LIBDIR = ROOT / "cocofest_b200" / "csrc"
+GOLD = json.loads((Path(__file__).parent / "golden" / "ivp_golden.json").read_text())
+
+
+@pytest.fixture(scope="module")
+def client():
+    assert (LIBDIR / "libfes_b200.so").exists(), "build first: python -c 'import __graft_entry__ as g; g.build()'"
+    subprocess.run(["gcc", "-O1", "-Wall", "-Wextra", "-Werror", "-std=c11", f"-I{ROOT / 'include'}", "-o", str(EXE), str(SRC),
+                    f"-L{LIBDIR}", "-lfes_b200", f"-Wl,-rpath,{LIBDIR}"], check=True)
+    return str(EXE)
+
+
+def test_library_is_self_contained_and_refuses_bad_arguments(client):
+    deps = subprocess.run(["ldd", str(LIBDIR / "libfes_b200.so")], capture_output=True, text=True, check=True).stdout
+    assert "torch" not in deps and "python" not in deps.lower()
+    r = subprocess.run([client, "--errors"], capture_output=True, text=True)
+    assert r.returncode == 0, r.stdout + r.stderr
+    assert "refused 10 of 10" in r.stdout
+
+
+@pytest.mark.skipif(torch.cuda.is_available(), reason="checks the behaviour WITHOUT a device")
+def test_plain_c_call_fails_loudly_without_a_device(client):
+    r = subprocess.run([client], capture_output=True, text=True)
+    assert r.returncode == 10 and "fes_ivp_host_f64 ->" in r.stderr and r.stdout == ""
+
+
+@pytest.mark.gpu
+def test_plain_c_call_reproduces_the_reference_golden(client):
+    r = subprocess.run([client], capture_output=True, text=True)
+    assert r.returncode == 0, r.stderr
+    force = np.array([float(x) for x in r.stdout.split()])
+    np.testing.assert_almost_equal(force, np.array(GOLD["F"]["ding2003_with_fatigue"]), decimal=GOLD["decimal"])
