@@ -360,7 +360,9 @@ def main():
         threads = host_threads()
         n_traj, n_int = size_cpu_sample(proto, threads, target_s=12.0)
         rate, secs = cpu_reference_rate(proto, n_traj, n_int, threads)
+        rate1, secs1 = cpu_reference_rate(proto, max(1, n_traj // max(threads, 1) // 4), n_int, 1)  # scalar row, SURVEY 8d (ii)
         cpu = {"value": rate, "unit": UNIT, "cores": threads, "kind": "port", "seconds": secs,
+               "single_thread": {"value": rate1, "seconds": secs1},
                "sample": f"{n_traj} trajectories x first {n_int} intervals ({n_int * 10} RK4 steps) with d x/d x0, "
                          "reference formulation (N-term exp sum per RHS, dual-number tangents), OpenMP over trajectories"}
 
