@@ -290,18 +290,18 @@ def main():
     # ---- end-to-end arm: public API with HOST buffers (H2D + kernels + D2H inside the timed region) -----
     e2e = None
     if not args.no_e2e:
-        def e2e_step():
+        def e2e_step(out=None):
             r = fes.ivp(fes.FES_DING2003, True, params_h, x0_h, win_h, proto["dt"], n_steps=S, n_shooting=ns,
-                        dirs=fes.FES_DIR_X0, trace="nodes", trace_batch=trace_B)
+                        dirs=fes.FES_DIR_X0, trace="nodes", trace_batch=trace_B, out=out)
             return r
 
-        for _ in range(2):  # warm torch's caching pinned-host allocator and the stream-ordered device pool
-            r = e2e_step()
+        r = None
+        for _ in range(2):  # allocates the pinned result buffers once and warms the stream-ordered device pool
+            r = e2e_step(r)
         barrier()
         t0 = time.perf_counter()
         for _ in range(args.steps):
-            r = None  # the previous step's pinned result buffers return to the caching allocator
-            r = e2e_step()
+            r = e2e_step(r)  # results land in the same pinned host buffers, as a solver loop would keep them
         torch.cuda.synchronize()
         el = time.perf_counter() - t0
         t = torch.tensor([el], dtype=torch.float64, device=dev)

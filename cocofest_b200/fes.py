@@ -210,13 +210,16 @@ def direction_columns(kind, fatigue, dirs, N=0, tile_offset=0):
 
 
 def ivp(kind, fatigue, params, x0, win, dt, n_steps=10, ctrl=None, n_shooting=None, scheme=4, dirs=0, t_start=0.0,
-        tauc=None, r0_km=R0_KM_RELATIONSHIP, trace="none", trace_batch=None, sens_trace=False, dtype=None) -> IvpResult:
+        tauc=None, r0_km=R0_KM_RELATIONSHIP, trace="none", trace_batch=None, sens_trace=False, dtype=None,
+        out: "IvpResult | None" = None) -> IvpResult:
     """Integrates B trajectories over ``n_shooting`` intervals of length ``dt`` with ``n_steps`` RK steps each.
 
     params [14] | [14,B];  x0 [nx,B];  win [>=ns,N] | [>=ns,N,B] (float64);  ctrl None | [ns,nu] | [ns,nu,B].
     dirs: 0 | FES_DIR_X0 | FES_DIR_P | FES_DIR_P|FES_DIR_PF  -> chained sensitivities d x(t) / d (x0 | params).
     trace: "none" | "nodes" (ns+1 points) | "steps" (ns*S+1 points, the IvpFes.integrate layout), for the
     first ``trace_batch`` trajectories (default: all).
+    out: an ``IvpResult`` of an earlier call with the same shapes, whose tensors are overwritten instead of
+    allocating new ones (repeated calls from a solver loop; pinned host buffers are expensive to allocate).
     """
     x0 = torch.as_tensor(x0)
     device, dtype, B, N, flags, params, win, ctrl = _common(kind, fatigue, params, win, ctrl, x0, dtype)
@@ -239,10 +242,17 @@ def ivp(kind, fatigue, params, x0, win, dt, n_steps=10, ctrl=None, n_shooting=No
     npts = ns * n_steps + 1 if trace_every == 1 else ns + 1
     desc = _desc(kind, fatigue, scheme, N, ns, n_steps, dirs, flags, B, dt, t_start, tauc, r0_km,
                  trace_every=trace_every, trace_batch=tB)
-    out_x = _empty((nx, B), dtype, device)
-    out_tr = _empty((npts, nx, tB), dtype, device) if (trace != "none" and tB) else None
-    out_sf = _empty((nx, nd, B), dtype, device) if nd else None
-    out_st = _empty((ns + 1, nx, nd, tB), dtype, device) if (nd and sens_trace and tB) else None
+    def buf(old, shape):
+        if old is None:
+            return _empty(shape, dtype, device)
+        if tuple(old.shape) != tuple(shape) or old.dtype != dtype or old.device != device or not old.is_contiguous():
+            raise ValueError(f"out: expected a contiguous {dtype} tensor of shape {tuple(shape)} on {device}")
+        return old
+
+    out_x = buf(out and out.x_final, (nx, B))
+    out_tr = buf(out and out.trace, (npts, nx, tB)) if (trace != "none" and tB) else None
+    out_sf = buf(out and out.sens_final, (nx, nd, B)) if nd else None
+    out_st = buf(out and out.sens_trace, (ns + 1, nx, nd, tB)) if (nd and sens_trace and tB) else None
     L = _lib.lib()
     is32 = dtype == torch.float32
     buf = FesIvpBuffers(_ptr(params), _ptr(x0), _ptr(win), _ptr(ctrl), _ptr(out_x), _ptr(out_tr), _ptr(out_sf),

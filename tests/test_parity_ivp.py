@@ -227,3 +227,21 @@ def test_ivp_window_of_pads_only_is_pure_decay(backend):
     z = -(dt / S) / fo.default_tauc(kind)
     amp = (1 + z + z * z / 2 + z ** 3 / 6 + z ** 4 / 24) ** (ns * S)
     assert abs(got[0, 0] / (0.5 * amp) - 1) < 1e-12
+
+
+@pytest.mark.parametrize("backend", BACKENDS, indirect=True)
+def test_ivp_out_buffers_are_reused(backend):
+    pb = random_problem("ding2003_with_fatigue", B=9, seed=2)
+    params, x0, win, ctrl = to_lib(pb, backend)
+    kw = dict(n_shooting=pb["ns"], dirs=fes.FES_DIR_X0, trace="nodes", sens_trace=True)
+    a = fes.ivp(pb["kind"], pb["fat"], params, x0, win, pb["dt"], **kw)
+    ref = [t.clone() for t in (a.x_final, a.trace, a.sens_final, a.sens_trace)]
+    ptrs = [t.data_ptr() for t in (a.x_final, a.trace, a.sens_final, a.sens_trace)]
+    for t in (a.x_final, a.trace, a.sens_final, a.sens_trace):
+        t.zero_()
+    b = fes.ivp(pb["kind"], pb["fat"], params, x0, win, pb["dt"], out=a, **kw)
+    got = (b.x_final, b.trace, b.sens_final, b.sens_trace)
+    assert [t.data_ptr() for t in got] == ptrs
+    assert all(torch.equal(g, r) for g, r in zip(got, ref))
+    with pytest.raises(ValueError, match="out: expected"):
+        fes.ivp(pb["kind"], pb["fat"], params, x0, win, pb["dt"], out=a, **{**kw, "n_shooting": pb["ns"] - 1})
