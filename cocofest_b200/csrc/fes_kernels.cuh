@@ -40,6 +40,9 @@ constexpr int min_blocks() {
     // same effect on the two-state kernels (Hmed P columns: 182 registers unconstrained, +16 % under the 204 cap,
     // profiles/r01_tune_ident_g.txt); the dense fatigue parameter columns (P, P|PF: 204-254 registers) stay free
     constexpr bool red = FAT && (GROUPS == G_X0 || GROUPS == G_U || GROUPS == G_W || (GROUPS == (G_X0 | G_U) && KIND == DING2007));
+    // Ding2007 parameter columns (config 3): 7 resident blocks = 120 registers, no spill, +4 % over the 138-register build;
+    // every other kernel moved by < 1.5 % or lost (profiles/r01_tune_min_blocks_m.txt)
+    if (sizeof(T) == 8 && !FAT && KIND == DING2007 && GROUPS == G_P) return 7;
     return (sizeof(T) == 8 && (red || !FAT)) ? 5 : 2;
 #endif
 }
