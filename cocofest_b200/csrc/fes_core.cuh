@@ -497,13 +497,13 @@ FES_HD void rk_step_scheme(const Traj<T> &tr, const Interval<T, Dirs<KIND, FAT, 
         dKm = x[4] - tr.km_rest;
     }
 
-    static_for<0, NS>([&](auto is) {
+    // the two halves of a stage: the nominal RHS (fills the Jacobian record st) and the tangent columns (consume it)
+    auto nominal_stage = [&](auto is, Stage<T> &st) {
         constexpr int s = decltype(is)::value;
         constexpr bool LAST = s == NS - 1;
         const T hb = h * T(TB::beta(s));
         const T ha = h * T(LAST ? 0.0 : TB::alpha(s + 1));
         const T eps = e[TB::eps_at(s)];
-        Stage<T> st;
         {
             T k[NX];
             nominal_rhs<T, KIND, FAT, NEED>(tr, Etc * eps, iv.g, xs, k, st);
@@ -523,6 +523,13 @@ FES_HD void rk_step_scheme(const Traj<T> &tr, const Interval<T, Dirs<KIND, FAT, 
                 if constexpr (!LAST) xs[j] = xfma(ha, k[j], x[j]);
             }
         }
+    };
+    auto column_stage = [&](auto is, const Stage<T> &st) {
+        constexpr int s = decltype(is)::value;
+        constexpr bool LAST = s == NS - 1;
+        const T hb = h * T(TB::beta(s));
+        const T ha = h * T(LAST ? 0.0 : TB::alpha(s + 1));
+        const T eps = e[TB::eps_at(s)];
         T mu_s = T(0), nu_s = T(0);
         if constexpr (MODES) {
             mu_s = (T)mus;
@@ -552,7 +559,24 @@ FES_HD void rk_step_scheme(const Traj<T> &tr, const Interval<T, Dirs<KIND, FAT, 
                 if constexpr (!LAST) vs[d][j] = xfma(ha, k[j], tg.V[d][j]);
             }
         });
+    };
+#ifdef FES_NOMINAL_AHEAD
+    // experiment: issue the nominal chain of stage s+1 (which depends only on the nominal stage s) ahead of the
+    // columns of stage s, so that its reciprocal chain overlaps their FMAs; two Stage records are live
+    Stage<T> stq[2];
+    nominal_stage(std::integral_constant<int, 0>{}, stq[0]);
+    static_for<0, NS>([&](auto is) {
+        constexpr int s = decltype(is)::value;
+        if constexpr (s + 1 < NS) nominal_stage(std::integral_constant<int, s + 1>{}, stq[(s + 1) & 1]);
+        column_stage(is, stq[s & 1]);
     });
+#else
+    static_for<0, NS>([&](auto is) {
+        Stage<T> st;
+        nominal_stage(is, st);
+        column_stage(is, st);
+    });
+#endif
 #pragma unroll
     for (int j = 0; j < NXN; ++j) x[j] = xn[j];
     if constexpr (FAT) {
