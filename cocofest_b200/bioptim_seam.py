@@ -151,7 +151,12 @@ class FesIntegrator:
 def as_casadi_function(integrator: FesIntegrator, name="integrator"):
     """casadi Function with bioptim's integrator signature whose evaluation and first derivatives come from
     ``integrator``.  Only first-order sensitivities exist: run Ipopt with
-    ``Solver.IPOPT(_hessian_approximation="limited-memory")``."""
+    ``Solver.IPOPT(_hessian_approximation="limited-memory")``.
+
+    Derivative blocks supplied: d xf / d (x0, u, p).  The blocks of ``xall`` and the columns of ``t_span`` and ``d``
+    are declared structurally zero: bioptim's continuity constraint reads ``xf`` only (penalty.py:1092-1099), cocofest
+    fixes the phase time and passes the stimulation window as numerical data.  A problem that puts ``xall`` or a free
+    phase time into a constraint or objective must not use this wrapper."""
     try:
         import casadi
     except ImportError as e:  # pragma: no cover - casadi is absent from this image

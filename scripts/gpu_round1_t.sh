@@ -1,0 +1,15 @@
+#!/bin/bash
+# twentieth GPU pass: identify kernel compiled for 5 / 6 resident blocks (168 registers + spills) against the default (253)
+set -x
+mkdir -p gpurun_out
+V=cocofest_b200/csrc/build
+: > gpurun_out/tune_t.txt
+for d in default $V/var_t_*/; do
+  if [ "$d" = default ]; then name=default; lib=$PWD/cocofest_b200/csrc/libfes_b200.so; else name=$(basename $d); lib=$PWD/$d/libfes_b200.so; fi
+  FES_B200_LIB=$lib timeout 300 python scripts/bench_configs.py --configs 4 2>/dev/null | python -c '
+import sys, json
+for l in sys.stdin:
+    d = json.loads(l)
+    if "config" in d: print("'$name'", d["config"][:3], "%.4e" % d["value"], "%.4f" % d["ms_per_step"])' >> gpurun_out/tune_t.txt
+done
+cat gpurun_out/tune_t.txt
