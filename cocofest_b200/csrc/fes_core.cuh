@@ -178,7 +178,10 @@ FES_HD void load_traj(Traj<T> &tr, PF p, T tauc, T r0_km) {
     tr.alpha_a = p(P_ALPHA_A);
     tr.alpha_tau1 = p(P_ALPHA_TAU1);
     tr.alpha_km = p(P_ALPHA_KM);
-    tr.kappa = T(1) / p(P_TAU_FAT);
+    // reciprocal without the IEEE-division slow path (once per (scenario, interval) in shoot); a non-finite or huge
+    // tau_fat (fatigue switched off by the caller) takes the exact division
+    const T tf = p(P_TAU_FAT);
+    tr.kappa = (xabs(tf) <= T(3.0e38)) ? xrcp(tf) : T(1) / tf;
     tr.kappa2 = tr.kappa * tr.kappa;
     tr.a_rest_k = tr.a_rest * tr.kappa;
     tr.tau1_rest_k = tr.tau1_rest * tr.kappa;
@@ -190,7 +193,7 @@ FES_HD void load_traj(Traj<T> &tr, PF p, T tauc, T r0_km) {
     tr.bs = p(P_BS);
     tr.Is = p(P_IS);
     tr.cr = p(P_CR);
-    tr.inv_tauc = T(1) / tauc;
+    tr.inv_tauc = xrcp(tauc);
 }
 
 // ---- per-interval quantities ------------------------------------------------------------------
@@ -220,7 +223,7 @@ FES_HD void interval_setup(const Traj<T> &tr, TF tab, CF ctl, int N, int tile_of
     if constexpr (KIND == DING2007) {
         // a_calculation, ding2007.py:188; the control is the width of the LAST pulse (ding2007.py:280)
         const T pw = ctl(0);
-        const T ipdt = T(1) / tr.pdt;
+        const T ipdt = xrcp(tr.pdt);
         const T z = (pw - tr.pd0) * ipdt;
         const T ew = xexp(-z);
         iv.g = T(1) - ew;

@@ -257,8 +257,11 @@ FES_HD void ident_candidate(const IdentArgs<T> &a, int64_t b, const T *eps, T *a
 
 #if defined(__CUDACC__)
 
+// Resident blocks the compiler must make room for.  6 blocks of 64 threads cap the kernel at 168 registers: the Hmed
+// instance then spills ~1 KB per thread to (L1-resident) local memory, and still gains 4.5 % over the 253-register /
+// 4-block build because 12 warps instead of 8 cover the dependent-issue latency (profiles/r01_tune_ident_t.txt).
 #ifndef FES_IDENT_MIN_BLOCKS  // sweep knob (scripts/build_variants.sh)
-#define FES_IDENT_MIN_BLOCKS 2
+#define FES_IDENT_MIN_BLOCKS 6
 #endif
 template <typename T, int KIND>
 __global__ void __launch_bounds__(BLOCK, FES_IDENT_MIN_BLOCKS) fes_ident_kernel(const IdentArgs<T> a) {
