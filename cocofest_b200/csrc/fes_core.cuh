@@ -89,6 +89,23 @@ constexpr bool dir_has_cn(int c) {
     return c == D_CN0 || c == D_INT || c == D_WT || c == D_KM_REST || c == D_AR || c == D_BS || c == D_IS || c == D_CR;
 }
 constexpr bool dir_has_dg(int c) { return c == D_PW || c == D_PD0 || c == D_PDT; }
+// Columns whose Cn component is FORCED through the pulse sum (vCn' = (sE eps(t) - vCn)/tauc, sE constant over the
+// interval).  That row is linear and identical for all of them, so over one RK step
+//     vCn(stage s) = c dl_s + sE psi_s,     vCn(end) = c dl_NS + sE psi_NS        (c = vCn at the step start)
+// with dl = the scheme's stage values of v' = -v/tauc from 1 (loop-invariant) and psi = those of
+// psi' = (eps - psi)/tauc from 0 (shared by every column of the step).  Explicit RK maps are linear in (c, sE) on a
+// linear row, so this IS the tangent of the discrete map; the column stores c only and its F-row takes two FMAs.
+constexpr bool dir_forced_cn(int c) { return dir_has_cn(c) && c != D_CN0; }
+// The shared modes cost ~20 instructions per step (psi 12, the two products per stage 8) and save ~10 per forced column:
+// used from three such columns on (Hmed parameter / intensity tiles, pulse-time tiles); below that each column
+// integrates its own Cn component (Ding2003 / Ding2007 km_rest column: 202 instead of 213 instructions per step).
+template <class D>
+constexpr bool dirs_forced_cn() {
+    int n = 0;
+    for (int d = 0; d < D::ND; ++d)
+        if (dir_forced_cn(D::code(d))) ++n;
+    return n >= 3;
+}
 // Fatigue models: the rows A', Tau1', Km' are linear with the SAME decay 1/tau_fat and are all driven by F
 // alone, so for every direction that does not force those rows (initial states, controls, pulse times) the
 // tangent (vA, vTau1, vKm) stays in a 1-dimensional affine family:
@@ -326,17 +343,21 @@ FES_HD void nominal_rhs(const Traj<T> &tr, T Ee, T g, const T *x, T *k, Stage<T>
 }
 
 // ---- one RK stage of one tangent column -----------------------------------------------------
-template <typename T, int KIND, bool FAT, int CODE>
-FES_HD void column_rhs(const Traj<T> &tr, const Stage<T> &st, T eps, T sE, T dg, const T *v, T *k) {
-    constexpr bool CN = dir_has_cn(CODE);
-    if constexpr (CN) {
-        if constexpr (CODE == D_CN0) k[0] = -(v[0] * tr.inv_tauc);
-        else k[0] = xfma(sE, eps, -v[0]) * tr.inv_tauc;
-    } else {
-        k[0] = T(0);
-    }
+// pc_dl = cCn dl_s, pc_psi = cCn psi_s (forced-Cn columns, see dir_forced_cn; S0: first stage, psi_0 = 0);
+// v[0] of such a column is its Cn component at the step start and k[0] is not produced.
+// SH: the forced Cn components of this direction set use the shared modes.
+template <typename T, int KIND, bool FAT, int CODE, bool S0, bool SH>
+FES_HD void column_rhs(const Traj<T> &tr, const Stage<T> &st, T eps, T sE, T dg, T pc_dl, T pc_psi, const T *v, T *k) {
+    constexpr bool OWN = CODE == D_CN0 || (dir_forced_cn(CODE) && !SH);  // integrates its own Cn component
+    if constexpr (CODE == D_CN0) k[0] = -(v[0] * tr.inv_tauc);
+    else if constexpr (OWN) k[0] = xfma(sE, eps, -v[0]) * tr.inv_tauc;
+    else k[0] = T(0);
     T kf = st.cF * v[1];
-    if constexpr (CN) kf = xfma(st.cCn, v[0], kf);
+    if constexpr (OWN) kf = xfma(st.cCn, v[0], kf);
+    if constexpr (dir_forced_cn(CODE) && SH) {
+        kf = xfma(pc_dl, v[0], kf);
+        if constexpr (!S0) kf = xfma(pc_psi, sE, kf);
+    }
     if constexpr (FAT) {
         kf = xfma(st.cA, v[2], kf);
         kf = xfma(st.cT1, v[3], kf);
@@ -372,12 +393,15 @@ FES_HD void column_rhs(const Traj<T> &tr, const Stage<T> &st, T eps, T sE, T dg,
 
 // ---- one RK stage of one REDUCED tangent column (fatigue models, see dir_reduced) ------------
 // v = (vCn, vF, W); mu / nu = the shared decaying scalars (fatigue mode, Cn mode) at this stage point.
-template <typename T, int KIND, int CODE>
-FES_HD void column_rhs_red(const Traj<T> &tr, const Stage<T> &st, T eps, T sE, T dg, T mu, T nu, const T *v, T *k) {
+template <typename T, int KIND, int CODE, bool S0, bool SH>
+FES_HD void column_rhs_red(const Traj<T> &tr, const Stage<T> &st, T eps, T sE, T dg, T pc_dl, T pc_psi, T mu, T nu, const T *v, T *k) {
     T kf = xfma(st.cW, v[2], st.cF * v[1]);
     if constexpr (CODE == D_CN0) {
         kf = xfma(st.cCn, nu, kf);
-    } else if constexpr (dir_has_cn(CODE)) {
+    } else if constexpr (dir_forced_cn(CODE) && SH) {
+        kf = xfma(pc_dl, v[0], kf);
+        if constexpr (!S0) kf = xfma(pc_psi, sE, kf);
+    } else if constexpr (dir_forced_cn(CODE)) {
         k[0] = xfma(sE, eps, -v[0]) * tr.inv_tauc;
         kf = xfma(st.cCn, v[0], kf);
     }
@@ -500,6 +524,23 @@ FES_HD void rk_step_scheme(const Traj<T> &tr, const Interval<T, Dirs<KIND, FAT, 
         dKm = x[4] - tr.km_rest;
     }
 
+    // shared modes of the forced Cn components (dir_forced_cn): dl[s] = stage values of v' = -v/tauc from 1
+    // (loop-invariant), psi = stage values of psi' = (eps - psi)/tauc from 0
+    constexpr bool CNF = dirs_forced_cn<D>();
+    T dl[NS + 1];
+    T psi_s = T(0), psi_n = T(0);
+    if constexpr (CNF) {
+        const T zt = tr.inv_tauc * h;
+        dl[0] = T(1);
+        T acc = T(1);
+        static_for<0, NS>([&](auto is) {
+            constexpr int s = decltype(is)::value;
+            if constexpr (TB::beta(s) != 0.0) acc = xfma(-zt * T(TB::beta(s)), dl[s], acc);
+            if constexpr (s + 1 < NS) dl[s + 1] = xfma(-zt * T(TB::alpha(s + 1)), dl[s], T(1));
+        });
+        dl[NS] = acc;
+    }
+
     // the two halves of a stage: the nominal RHS (fills the Jacobian record st) and the tangent columns (consume it)
     auto nominal_stage = [&](auto is, Stage<T> &st) {
         constexpr int s = decltype(is)::value;
@@ -546,16 +587,25 @@ FES_HD void rk_step_scheme(const Traj<T> &tr, const Interval<T, Dirs<KIND, FAT, 
                 nus = fma(-zc * TB::alpha(s + 1), nus, tg.nu);
             }
         }
+        T pc_dl = T(0), pc_psi = T(0);
+        if constexpr (CNF) {
+            pc_dl = s == 0 ? st.cCn : st.cCn * dl[s];
+            if constexpr (s > 0) pc_psi = st.cCn * psi_s;
+            const T kpsi = s == 0 ? eps * tr.inv_tauc : (eps - psi_s) * tr.inv_tauc;
+            if constexpr (TB::beta(s) != 0.0) psi_n = s == 0 ? hb * kpsi : xfma(hb, kpsi, psi_n);
+            if constexpr (!LAST) psi_s = ha * kpsi;
+        }
         static_for<0, ND>([&](auto ic) {
             constexpr int d = decltype(ic)::value;
             constexpr int C = D::code(d);
-            // stored components of this column: Cn only for the directions that reach it; (vF, W) when reduced
-            constexpr int J0 = dir_first(FAT, C), J1 = dir_last(FAT, C);
+            // stored components of this column: Cn only for the directions that reach it; (vF, W) when reduced;
+            // a forced Cn component (vs[d][0] = its value at the step start) is advanced once, after the stages
+            constexpr int J0 = (CNF && dir_forced_cn(C)) ? 1 : dir_first(FAT, C), J1 = dir_last(FAT, C);
             T k[NX];
             if constexpr (dir_reduced(FAT, C))
-                column_rhs_red<T, KIND, C>(tr, st, eps, iv.sE[d], iv.dg[d], mu_s, nu_s, vs[d], k);
+                column_rhs_red<T, KIND, C, s == 0, CNF>(tr, st, eps, iv.sE[d], iv.dg[d], pc_dl, pc_psi, mu_s, nu_s, vs[d], k);
             else
-                column_rhs<T, KIND, FAT, C>(tr, st, eps, iv.sE[d], iv.dg[d], vs[d], k);
+                column_rhs<T, KIND, FAT, C, s == 0, CNF>(tr, st, eps, iv.sE[d], iv.dg[d], pc_dl, pc_psi, vs[d], k);
 #pragma unroll
             for (int j = J0; j < J1; ++j) {
                 if constexpr (TB::beta(s) != 0.0) vn[d][j] = xfma(hb, k[j], vn[d][j]);
@@ -590,8 +640,9 @@ FES_HD void rk_step_scheme(const Traj<T> &tr, const Interval<T, Dirs<KIND, FAT, 
     static_for<0, ND>([&](auto ic) {
         constexpr int d = decltype(ic)::value;
         constexpr int C = D::code(d);
+        if constexpr (CNF && dir_forced_cn(C)) tg.V[d][0] = xfma(tg.V[d][0], dl[NS], iv.sE[d] * psi_n);
 #pragma unroll
-        for (int j = dir_first(FAT, C); j < dir_last(FAT, C); ++j) tg.V[d][j] = vn[d][j];
+        for (int j = (CNF && dir_forced_cn(C)) ? 1 : dir_first(FAT, C); j < dir_last(FAT, C); ++j) tg.V[d][j] = vn[d][j];
     });
     if constexpr (MODES) {
         tg.mu = mun;
