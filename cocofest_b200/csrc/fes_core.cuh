@@ -226,9 +226,22 @@ struct Interval {
 //   wa_i = exp(-(t_k - t_i)/tauc),  wb_i = exp(-(t_i - t_{i-1})/tauc) wa_i (0 for i = 0),  a = sum wa, b = sum wb
 //   so that  E = sum_i lambda_i (wa_i + (r0 - 1) wb_i)   [= a + (r0 - 1) b when lambda = 1].
 // tab(c) / ctl(c) return element c of this trajectory's row for the current node.
+// Hmed2018: tanh(bs (I - Is)) of the window slots of the previous interval, keyed by the intensity itself.  The
+// window slides by at most a few pulses per node, so slot i of a node usually holds the intensity that slot i or
+// i + 1 held at the previous node; its tanh (the one expensive operation of the set-up, N of them per interval) is
+// then reused -- the very same number, whatever pulse it belongs to.  Lives in per-thread local memory; reset
+// whenever bs or Is change (every cost evaluation of fes_identify).
+template <typename T>
+struct LamCache {
+    T I[66], th[66];
+    FES_HD void reset(int N) {
+        for (int i = 0; i <= N; ++i) I[i] = T(NAN);  // NaN never compares equal: nothing cached
+    }
+};
+
 template <typename T, int KIND, bool FAT, int GROUPS, class TF, class CF>
 FES_HD void interval_setup(const Traj<T> &tr, TF tab, CF ctl, int N, int tile_off,
-                           Interval<T, Dirs<KIND, FAT, GROUPS>::ND> &iv) {
+                           Interval<T, Dirs<KIND, FAT, GROUPS>::ND> &iv, LamCache<T> *lc = nullptr) {
     using D = Dirs<KIND, FAT, GROUPS>;
     constexpr int ND = D::ND;
     static_for<0, ND>([&](auto ic) {
@@ -266,8 +279,23 @@ FES_HD void interval_setup(const Traj<T> &tr, TF tab, CF ctl, int N, int tile_of
             const T W = xfma(tr.r0m1, wb, wa);
             T lam = T(1), th = T(0), du = T(0);
             if constexpr (KIND == HMED2018) {
-                du = ctl(i) - tr.Is;
-                th = xtanh(tr.bs * du);          // lambda_i_calculation, hmed2018.py:179
+                const T Ii = ctl(i);
+                du = Ii - tr.Is;
+                bool hit = false;
+                if (lc != nullptr) {
+                    if (lc->I[i] == Ii) {
+                        th = lc->th[i];
+                        hit = true;
+                    } else if (lc->I[i + 1] == Ii) {
+                        th = lc->th[i + 1];
+                        hit = true;
+                    }
+                }
+                if (!hit) th = xtanh(tr.bs * du);  // lambda_i_calculation, hmed2018.py:179
+                if (lc != nullptr) {
+                    lc->I[i] = Ii;
+                    lc->th[i] = th;
+                }
                 lam = tr.ar * (th + tr.cr);
             }
             E = xfma(lam, W, E);

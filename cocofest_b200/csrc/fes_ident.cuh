@@ -64,6 +64,14 @@ FES_HD void ident_eval(const IdentArgs<T> &a, int64_t b, const T *pc, int pstrid
     }
     Tangent<T, KIND, false, G_P> tg;
     tg.init();
+    LamCache<T> *lcp = nullptr;
+    [[maybe_unused]] LamCache<T> lc;
+#ifndef FES_IDENT_NO_LAMCACHE
+    if constexpr (KIND == HMED2018) {  // bs and Is differ from the previous evaluation: start empty
+        lc.reset(a.N);
+        lcp = &lc;
+    }
+#endif
     cost = T(0);
     T *g = acc, *H = acc + NPK * stride;
     static_for<0, NPK + I::NH>([&](auto ic) { acc[decltype(ic)::value * stride] = T(0); });
@@ -89,7 +97,7 @@ FES_HD void ident_eval(const IdentArgs<T> &a, int64_t b, const T *pc, int pstrid
         const T *crow = a.ctrl + (int64_t)node * a.nu * a.cB + b * a.cS;
         Interval<T, NPK> iv;
         interval_setup<T, KIND, false, G_P>(
-            tr, [&](int c) { return trow[c * a.tB]; }, [&](int c) { return crow[c * a.cB]; }, a.N, 0, iv);
+            tr, [&](int c) { return trow[c * a.tB]; }, [&](int c) { return crow[c * a.cB]; }, a.N, 0, iv, lcp);
         for (int i = 0; i < a.S; ++i)
             rk_step<T, KIND, false, G_P>(tr, iv, a.scheme, a.h, eps[2 * i], eps[2 * i + 1], eps[2 * i + 2], x, tg);
         fold(node + 1);

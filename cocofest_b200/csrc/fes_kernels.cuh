@@ -129,6 +129,12 @@ __global__ void FES_LAUNCH_BOUNDS fes_ivp_kernel(const IvpArgs<T> a) {
     for (int j = 0; j < NX; ++j) x[j] = a.x0[j * a.B + bb];
     Tangent<T, KIND, FAT, GROUPS> tg;
     tg.init();
+    LamCache<T> *lcp = nullptr;
+    [[maybe_unused]] LamCache<T> lc;
+    if constexpr (KIND == HMED2018) {
+        lc.reset(a.N);
+        lcp = &lc;
+    }
 
     const bool tr_on = live && a.trace_mode != 0 && b < a.trace_B;
     auto put_state = [&](int64_t pt) {
@@ -177,7 +183,7 @@ __global__ void FES_LAUNCH_BOUNDS fes_ivp_kernel(const IvpArgs<T> a) {
             }
             Interval<T, ND> iv;
             interval_setup<T, KIND, FAT, GROUPS>(
-                tr, [&](int c) { return trow[c * tstr]; }, [&](int c) { return crow[c * cstr]; }, a.N, a.tile_off, iv);
+                tr, [&](int c) { return trow[c * tstr]; }, [&](int c) { return crow[c * cstr]; }, a.N, a.tile_off, iv, lcp);
             for (int i = 0; i < a.S; ++i) {
                 rk_step<T, KIND, FAT, GROUPS>(tr, iv, a.scheme, a.h, s_eps[2 * i], s_eps[2 * i + 1], s_eps[2 * i + 2], x, tg);
                 if (tr_on && a.trace_mode == 1) put_state((int64_t)node * a.S + i + 1);

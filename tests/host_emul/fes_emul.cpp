@@ -71,12 +71,15 @@ int ivp_cpu(const IvpArgs<T> &a) {
                 });
         };
         if (tr_on) { put_state(0); put_sens(0); }
+        LamCache<T> lc;  // as fes_ivp_kernel: tanh of the previous interval's window slots (Hmed2018)
+        LamCache<T> *lcp = nullptr;
+        if (KIND == HMED2018) { lc.reset(a.N); lcp = &lc; }
         for (int node = 0; node < a.ns; ++node) {
             const T *trow = a.tab + (int64_t)node * a.row * a.tB + b * a.tS;
             const T *crow = a.ctrl + (int64_t)node * a.nu * a.cB + b * a.cS;
             Interval<T, ND> iv;
             interval_setup<T, KIND, FAT, GROUPS>(
-                tr, [&](int c) { return trow[c * a.tB]; }, [&](int c) { return crow[c * a.cB]; }, a.N, a.tile_off, iv);
+                tr, [&](int c) { return trow[c * a.tB]; }, [&](int c) { return crow[c * a.cB]; }, a.N, a.tile_off, iv, lcp);
             for (int i = 0; i < a.S; ++i) {
                 rk_step<T, KIND, FAT, GROUPS>(tr, iv, a.scheme, a.h, a.eps[2 * i], a.eps[2 * i + 1], a.eps[2 * i + 2], x, tg);
                 if (tr_on && a.trace_mode == 1) put_state((int64_t)node * a.S + i + 1);
