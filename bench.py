@@ -36,19 +36,20 @@ def flop_survey_per_step(nx=5, n_dir=5):
 def flop_alg_per_step():
     """ALGORITHMIC flops of one RK4 trajectory-step of the kernel's own (reduced) formulation, Ding2003 + fatigue with
     the 5 x0 columns -- DESIGN.md section 4 derives it line by line (+,-,*,reciprocal = 1, FMA = 2):
-      nominal stage   1 (E eps) + 15 (Cn', F' with the shared reciprocal) + 11 (Jacobian entries incl. cW)
-                                                                              = 27   x 4 stages = 108
-      nominal update  Cn, F: 2 states x (2 FMA x 3 stages + 1 FMA)                                =  28
+      nominal stage   13 (F' with the shared reciprocal; Cn' is never formed) + 11 (Jacobian entries incl. cW)
+                                                                              = 24   x 4 stages =  96
+      nominal Cn      Cn(stage) = Cn dl_s + E psi_s from the stage table: 3 x 3 stages + 3 after the step =  12
+      nominal update  F: 2 FMA x 3 stages + 1 FMA                                                  =  14
       nominal fatigue A, Tau1, Km reduced to the scalar Wn within the step (fes_core.cuh, rk_step_scheme):
                       Wn' 2 + Wn accumulate 2 + Wn stage 1 + 3 stage states x 2 FMA = 17 per middle stage,
                       14 first stage, 4 last stage, 12 to rebuild the three states                 =  64
       shared modes    2 scalars x (3 stage FMAs + 4 update FMAs)                                  =  28
       reduced column  stage: 5 (vF row; 3 for the F0 column) + 2 (W row); update 2 x 7 FMA = 28
                       -> 56 x 4 columns + 48 (F0)                                                  = 272
-    Total 500 (the shipped SASS executes 526: the reciprocal's three Newton FMAs count as one flop here).  It is
+    Total 486 (the shipped SASS executes 513: the reciprocal's three Newton FMAs count as one flop here).  It is
     lower than SURVEY 8d's 978 because the fatigue block of every tangent column collapses to one scalar W
-    (fes_core.cuh, dir_reduced); the survey figure is reported beside it."""
-    return 108 + 28 + 64 + 28 + 272
+    (fes_core.cuh, dir_reduced) and Cn rides on the tabulated modes; the survey figure is reported beside it."""
+    return 96 + 12 + 14 + 64 + 28 + 272
 
 
 class ClockSampler(threading.Thread):

@@ -64,7 +64,7 @@ inline Carve carve(const FesDesc *d, size_t tsize) {
     c.row = slot_tables(d->model_kind, d->dirs) ? 2 + 2 * d->n_trunc : 2;
     c.tB = (d->flags & FES_WIN_SHARED) ? 1 : d->batch;
     c.eps_off = 0;
-    c.tab_off = ((size_t)(2 * d->n_steps + 1) * tsize + 255) & ~(size_t)255;
+    c.tab_off = ((size_t)stage_table_len(d->n_steps) * tsize + 255) & ~(size_t)255;
     c.total = c.tab_off + (size_t)d->n_shooting * c.row * (size_t)c.tB * tsize;
     return c;
 }

@@ -60,11 +60,11 @@ int build_tables(const FesDesc *d, const double *win, void *ws, int64_t ws_bytes
     if (win == nullptr) return E_BUF;
     T *eps = reinterpret_cast<T *>((char *)ws + c.eps_off);
     T *tab = reinterpret_cast<T *>((char *)ws + c.tab_off);
-    const int64_t total = std::max<int64_t>((int64_t)d->n_shooting * c.tB, 2 * d->n_steps + 1);
+    const int64_t total = std::max<int64_t>((int64_t)d->n_shooting * c.tB, stage_table_len(d->n_steps));
     const unsigned grid = (unsigned)((total + 127) / 128);
     const int64_t wB = (d->flags & FES_WIN_SHARED) ? 1 : d->batch, wS = (d->flags & FES_WIN_SHARED) ? 0 : 1;
     fes_tables_kernel<T><<<grid, 128, 0, s>>>(win, wB, wS, d->n_trunc, d->n_shooting, c.row, d->dt, d->t_start, d->tauc,
-                                              tab, c.tB, d->n_steps, d->dt / d->n_steps, eps);
+                                              tab, c.tB, d->n_steps, d->dt / d->n_steps, d->scheme, eps);
     ++g_launches;
     return (int)cudaGetLastError();
 }

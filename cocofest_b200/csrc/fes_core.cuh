@@ -131,6 +131,30 @@ FES_HD void static_for(F &&f) {
     }
 }
 
+// ---- stage table: shared by every trajectory and interval of a call -------------------------------
+// [0, 2S]            eps_j  = exp(-(j h/2)/tauc), the decay of the pulse sum at the stage offsets
+// [2S+1 + 4 i + q]   psi    = the scheme's own integration of psi' = (eps - psi)/tauc over step i of the interval from
+//                    psi = 0: q = 0..2 its values at stages 1..3 (as many as the scheme has), q = 3 its value after
+//                    the step.  Every Cn-like linear row, x' = (g eps - x)/tauc with g constant over the interval,
+//                    is then  x(stage s) = x_i dl_s + g psi_s,  x_{i+1} = x_i dl_end + g psi_end  EXACTLY as the
+//                    scheme would integrate it (explicit RK maps are linear on linear rows): the nominal Cn (g = E)
+//                    and the forced Cn components of the tangent columns (g = sE) need no stages of their own.
+constexpr int stage_table_len(int S) { return 6 * S + 1; }
+FES_HD double stage_table_entry(int idx, int S, double h, double tauc, int scheme) {
+    if (idx <= 2 * S) return exp(-(0.5 * h * (double)idx) / tauc);
+    const int i = (idx - (2 * S + 1)) / 4, q = (idx - (2 * S + 1)) % 4;
+    const double z = h / tauc;
+    const double e0 = exp(-(h * (double)i) / tauc), e1 = exp(-(h * ((double)i + 0.5)) / tauc), e2 = exp(-(h * (double)(i + 1)) / tauc);
+    if (scheme == 1) return q == 3 ? z * e0 : 0.0;
+    const double p1 = 0.5 * z * e0;  // stage 1 value (RK2 midpoint and RK4)
+    if (scheme == 2) return q == 0 ? p1 : (q == 3 ? z * (e1 - p1) : 0.0);
+    const double k2 = e1 - p1, p2 = 0.5 * z * k2, k3 = e1 - p2, p3 = z * k3, k4 = e2 - p3;
+    if (q == 0) return p1;
+    if (q == 1) return p2;
+    if (q == 2) return p3;
+    return z * (e0 + 2.0 * k2 + 2.0 * k3 + k4) / 6.0;
+}
+
 // ---- scalar helpers ---------------------------------------------------------------------------
 FES_HD double xfma(double a, double b, double c) { return fma(a, b, c); }
 FES_HD float xfma(float a, float b, float c) { return fmaf(a, b, c); }
@@ -510,7 +534,7 @@ template <> struct Tableau<4> {
 // e[0], e[1], e[2] = eps at the step start, midpoint and end (relative to the interval start).
 template <typename T, int KIND, bool FAT, int GROUPS, int SCHEME>
 FES_HD void rk_step_scheme(const Traj<T> &tr, const Interval<T, Dirs<KIND, FAT, GROUPS>::ND> &iv, T h, const T *e,
-                           T *x, Tangent<T, KIND, FAT, GROUPS> &tg) {
+                           const T *ps, T *x, Tangent<T, KIND, FAT, GROUPS> &tg) {
     using D = Dirs<KIND, FAT, GROUPS>;
     using TB = Tableau<SCHEME>;
     constexpr int NX = D::NX;
@@ -530,7 +554,7 @@ FES_HD void rk_step_scheme(const Traj<T> &tr, const Interval<T, Dirs<KIND, FAT, 
     // the two shared decaying scalars of the reduced columns obey m' = -(z / h) m: same scheme, in double
     const double zf = (double)tr.kappa * (double)h, zc = (double)tr.inv_tauc * (double)h;
     double mus = tg.mu, mun = tg.mu, nus = tg.nu, nun = tg.nu;
-    const T Etc = iv.E * tr.inv_tauc;  // Cn' = (E eps - Cn)/tauc = Etc eps - Cn/tauc
+    // Cn' = (E eps - Cn)/tauc is a linear row with tabulated forcing: Cn(stage s) = Cn dl_s + E psi_s (stage table)
     // Nominal fatigue rows, reduced within the step exactly like the tangent ones: with the offsets d = x - rest at
     // the step start,  A(stage) = A_rest + dA m_s + alpha_a Wn,  Wn' = F - Wn/tau_fat (Wn = 0 at the step start),
     // m_s = the scheme's stage values of m' = -m/tau_fat from m = 1 (loop-invariant, hoisted by the compiler).
@@ -552,12 +576,11 @@ FES_HD void rk_step_scheme(const Traj<T> &tr, const Interval<T, Dirs<KIND, FAT, 
         dKm = x[4] - tr.km_rest;
     }
 
-    // shared modes of the forced Cn components (dir_forced_cn): dl[s] = stage values of v' = -v/tauc from 1
-    // (loop-invariant), psi = stage values of psi' = (eps - psi)/tauc from 0
+    // dl[s] = the scheme's stage values of v' = -v/tauc from 1 (loop-invariant); ps[s-1] = psi at stage s and ps[3] =
+    // psi after the step come from the stage table (stage_table_entry)
     constexpr bool CNF = dirs_forced_cn<D>();
     T dl[NS + 1];
-    T psi_s = T(0), psi_n = T(0);
-    if constexpr (CNF) {
+    {
         const T zt = tr.inv_tauc * h;
         dl[0] = T(1);
         T acc = T(1);
@@ -575,10 +598,9 @@ FES_HD void rk_step_scheme(const Traj<T> &tr, const Interval<T, Dirs<KIND, FAT, 
         constexpr bool LAST = s == NS - 1;
         const T hb = h * T(TB::beta(s));
         const T ha = h * T(LAST ? 0.0 : TB::alpha(s + 1));
-        const T eps = e[TB::eps_at(s)];
         {
             T k[NX];
-            nominal_rhs<T, KIND, FAT, NEED>(tr, Etc * eps, iv.g, xs, k, st);
+            nominal_rhs<T, KIND, FAT, NEED>(tr, T(0), iv.g, xs, k, st);  // k[0] is not used: Cn rides on the stage table
             if constexpr (FAT) {  // before xs[1] moves on: Wn' at this stage (k[2..4] of nominal_rhs are dead here)
                 const T kw = s == 0 ? xs[1] : xfma(-tr.kappa, wn_s, xs[1]);
                 if constexpr (TB::beta(s) != 0.0) wn_n = s == 0 ? hb * kw : xfma(hb, kw, wn_n);
@@ -589,8 +611,9 @@ FES_HD void rk_step_scheme(const Traj<T> &tr, const Interval<T, Dirs<KIND, FAT, 
                     xs[4] = xfma(tr.alpha_km, wn_s, xfma(dKm, fm[s + 1], tr.km_rest));
                 }
             }
+            if constexpr (!LAST) xs[0] = xfma(x[0], dl[s + 1], iv.E * ps[s]);
 #pragma unroll
-            for (int j = 0; j < NXN; ++j) {
+            for (int j = 1; j < NXN; ++j) {
                 if constexpr (TB::beta(s) != 0.0) xn[j] = xfma(hb, k[j], xn[j]);
                 if constexpr (!LAST) xs[j] = xfma(ha, k[j], x[j]);
             }
@@ -618,10 +641,7 @@ FES_HD void rk_step_scheme(const Traj<T> &tr, const Interval<T, Dirs<KIND, FAT, 
         T pc_dl = T(0), pc_psi = T(0);
         if constexpr (CNF) {
             pc_dl = s == 0 ? st.cCn : st.cCn * dl[s];
-            if constexpr (s > 0) pc_psi = st.cCn * psi_s;
-            const T kpsi = s == 0 ? eps * tr.inv_tauc : (eps - psi_s) * tr.inv_tauc;
-            if constexpr (TB::beta(s) != 0.0) psi_n = s == 0 ? hb * kpsi : xfma(hb, kpsi, psi_n);
-            if constexpr (!LAST) psi_s = ha * kpsi;
+            if constexpr (s > 0) pc_psi = st.cCn * ps[s - 1];
         }
         static_for<0, ND>([&](auto ic) {
             constexpr int d = decltype(ic)::value;
@@ -658,8 +678,9 @@ FES_HD void rk_step_scheme(const Traj<T> &tr, const Interval<T, Dirs<KIND, FAT, 
         column_stage(is, st);
     });
 #endif
+    x[0] = xfma(x[0], dl[NS], iv.E * ps[3]);
 #pragma unroll
-    for (int j = 0; j < NXN; ++j) x[j] = xn[j];
+    for (int j = 1; j < NXN; ++j) x[j] = xn[j];
     if constexpr (FAT) {
         x[2] = xfma(tr.alpha_a, wn_n, xfma(dA, fm[NS], tr.a_rest));
         x[3] = xfma(tr.alpha_tau1, wn_n, xfma(dT1, fm[NS], tr.tau1_rest));
@@ -668,7 +689,7 @@ FES_HD void rk_step_scheme(const Traj<T> &tr, const Interval<T, Dirs<KIND, FAT, 
     static_for<0, ND>([&](auto ic) {
         constexpr int d = decltype(ic)::value;
         constexpr int C = D::code(d);
-        if constexpr (CNF && dir_forced_cn(C)) tg.V[d][0] = xfma(tg.V[d][0], dl[NS], iv.sE[d] * psi_n);
+        if constexpr (CNF && dir_forced_cn(C)) tg.V[d][0] = xfma(tg.V[d][0], dl[NS], iv.sE[d] * ps[3]);
 #pragma unroll
         for (int j = (CNF && dir_forced_cn(C)) ? 1 : dir_first(FAT, C); j < dir_last(FAT, C); ++j) tg.V[d][j] = vn[d][j];
     });
@@ -681,11 +702,11 @@ FES_HD void rk_step_scheme(const Traj<T> &tr, const Interval<T, Dirs<KIND, FAT, 
 // e0, e1, e2 = eps at the step start, midpoint and end.  ONE uniform branch per step selects the scheme.
 template <typename T, int KIND, bool FAT, int GROUPS>
 FES_HD void rk_step(const Traj<T> &tr, const Interval<T, Dirs<KIND, FAT, GROUPS>::ND> &iv, int scheme, T h,
-                    T e0, T e1, T e2, T *x, Tangent<T, KIND, FAT, GROUPS> &tg) {
+                    T e0, T e1, T e2, const T *ps, T *x, Tangent<T, KIND, FAT, GROUPS> &tg) {
     const T e[3] = {e0, e1, e2};
-    if (scheme == 4) rk_step_scheme<T, KIND, FAT, GROUPS, 4>(tr, iv, h, e, x, tg);
-    else if (scheme == 2) rk_step_scheme<T, KIND, FAT, GROUPS, 2>(tr, iv, h, e, x, tg);
-    else rk_step_scheme<T, KIND, FAT, GROUPS, 1>(tr, iv, h, e, x, tg);
+    if (scheme == 4) rk_step_scheme<T, KIND, FAT, GROUPS, 4>(tr, iv, h, e, ps, x, tg);
+    else if (scheme == 2) rk_step_scheme<T, KIND, FAT, GROUPS, 2>(tr, iv, h, e, ps, x, tg);
+    else rk_step_scheme<T, KIND, FAT, GROUPS, 1>(tr, iv, h, e, ps, x, tg);
 }
 
 }  // namespace fes

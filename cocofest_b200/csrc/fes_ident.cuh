@@ -66,12 +66,12 @@ FES_HD void ident_eval(const IdentArgs<T> &a, int64_t b, const T *pc, int pstrid
     tg.init();
     LamCache<T> *lcp = nullptr;
     [[maybe_unused]] LamCache<T> lc;
-#ifndef FES_IDENT_NO_LAMCACHE
-    if constexpr (KIND == HMED2018) {  // bs and Is differ from the previous evaluation: start empty
+    // measured (profiles/r01_tune_ident_lamcache_x.txt): +2.5 % for the plain evaluation, -2.4 % inside the LM loop,
+    // where the cache would be refilled at every evaluation (bs and Is move) next to ~1.3 KB of register spills
+    if (KIND == HMED2018 && a.max_iter == 0) {
         lc.reset(a.N);
         lcp = &lc;
     }
-#endif
     cost = T(0);
     T *g = acc, *H = acc + NPK * stride;
     static_for<0, NPK + I::NH>([&](auto ic) { acc[decltype(ic)::value * stride] = T(0); });
@@ -99,7 +99,8 @@ FES_HD void ident_eval(const IdentArgs<T> &a, int64_t b, const T *pc, int pstrid
         interval_setup<T, KIND, false, G_P>(
             tr, [&](int c) { return trow[c * a.tB]; }, [&](int c) { return crow[c * a.cB]; }, a.N, 0, iv, lcp);
         for (int i = 0; i < a.S; ++i)
-            rk_step<T, KIND, false, G_P>(tr, iv, a.scheme, a.h, eps[2 * i], eps[2 * i + 1], eps[2 * i + 2], x, tg);
+            rk_step<T, KIND, false, G_P>(tr, iv, a.scheme, a.h, eps[2 * i], eps[2 * i + 1], eps[2 * i + 2],
+                                         eps + 2 * a.S + 1 + 4 * i, x, tg);
         fold(node + 1);
     }
 }
@@ -275,8 +276,8 @@ template <typename T, int KIND>
 __global__ void __launch_bounds__(BLOCK, FES_IDENT_MIN_BLOCKS) fes_ident_kernel(const IdentArgs<T> a) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     T *s_eps = reinterpret_cast<T *>(smem_raw);
-    T *s_acc = s_eps + ((2 * a.S + 1 + 3) & ~3);  // [ident_scratch][BLOCK]
-    for (int i = threadIdx.x; i < 2 * a.S + 1; i += BLOCK) s_eps[i] = a.eps[i];
+    T *s_acc = s_eps + ((stage_table_len(a.S) + 3) & ~3);  // [ident_scratch][BLOCK]
+    for (int i = threadIdx.x; i < stage_table_len(a.S); i += BLOCK) s_eps[i] = a.eps[i];
     __syncthreads();
     const int64_t b = (int64_t)blockIdx.x * BLOCK + threadIdx.x;
     if (b >= a.B) return;
@@ -286,7 +287,7 @@ __global__ void __launch_bounds__(BLOCK, FES_IDENT_MIN_BLOCKS) fes_ident_kernel(
 template <typename T, int KIND>
 int launch_ident_k(const IdentArgs<T> &a, cudaStream_t s) {
     const unsigned grid = (unsigned)((a.B + BLOCK - 1) / BLOCK);
-    const size_t smem = (((2 * a.S + 1 + 3) & ~3) + (size_t)ident_scratch<KIND>() * BLOCK) * sizeof(T);
+    const size_t smem = (((stage_table_len(a.S) + 3) & ~3) + (size_t)ident_scratch<KIND>() * BLOCK) * sizeof(T);
     fes_ident_kernel<T, KIND><<<grid, BLOCK, smem, s>>>(a);
     return (int)cudaGetLastError();
 }

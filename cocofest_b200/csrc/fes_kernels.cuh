@@ -82,9 +82,9 @@ struct ShootArgs {
 template <typename T>
 __global__ void fes_tables_kernel(const double *__restrict__ win, int64_t wB, int64_t wS, int N, int ns, int row,
                                   double dt, double t_start, double tauc, T *__restrict__ tab, int64_t tB,
-                                  int S, double h, T *__restrict__ eps) {
+                                  int S, double h, int scheme, T *__restrict__ eps) {
     const int64_t idx = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-    if (idx < 2 * S + 1) eps[idx] = (T)exp(-(0.5 * h * (double)idx) / tauc);
+    if (idx < stage_table_len(S)) eps[idx] = (T)stage_table_entry((int)idx, S, h, tauc, scheme);
     if (idx >= (int64_t)ns * tB) return;
     const int64_t node = idx / tB, b = idx % tB;
     const double tn = t_start + dt * (double)node;  // optimization_vector.py:373: t_k = dt * k
@@ -113,10 +113,10 @@ __global__ void FES_LAUNCH_BOUNDS fes_ivp_kernel(const IvpArgs<T> a) {
     constexpr int ND = D::ND;
     extern __shared__ __align__(16) unsigned char smem_raw[];
     T *s_eps = reinterpret_cast<T *>(smem_raw);
-    T *s_tab = s_eps + ((2 * a.S + 1 + 3) & ~3);
+    T *s_tab = s_eps + ((stage_table_len(a.S) + 3) & ~3);
     T *s_ctl = s_tab + (a.tS == 0 ? a.chunk * a.row : 0);
     const int tid = threadIdx.x;
-    for (int i = tid; i < 2 * a.S + 1; i += BLOCK) s_eps[i] = a.eps[i];
+    for (int i = tid; i < stage_table_len(a.S); i += BLOCK) s_eps[i] = a.eps[i];
 
     const int64_t b = (int64_t)blockIdx.x * BLOCK + tid;
     const bool live = b < a.B;
@@ -185,7 +185,8 @@ __global__ void FES_LAUNCH_BOUNDS fes_ivp_kernel(const IvpArgs<T> a) {
             interval_setup<T, KIND, FAT, GROUPS>(
                 tr, [&](int c) { return trow[c * tstr]; }, [&](int c) { return crow[c * cstr]; }, a.N, a.tile_off, iv, lcp);
             for (int i = 0; i < a.S; ++i) {
-                rk_step<T, KIND, FAT, GROUPS>(tr, iv, a.scheme, a.h, s_eps[2 * i], s_eps[2 * i + 1], s_eps[2 * i + 2], x, tg);
+                rk_step<T, KIND, FAT, GROUPS>(tr, iv, a.scheme, a.h, s_eps[2 * i], s_eps[2 * i + 1], s_eps[2 * i + 2],
+                                              s_eps + 2 * a.S + 1 + 4 * i, x, tg);
                 if (tr_on && a.trace_mode == 1) put_state((int64_t)node * a.S + i + 1);
             }
             if (tr_on) {
@@ -218,7 +219,7 @@ __global__ void FES_LAUNCH_BOUNDS fes_shoot_kernel(const ShootArgs<T> a) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     T *s_eps = reinterpret_cast<T *>(smem_raw);
     const int tid = threadIdx.x;
-    for (int i = tid; i < 2 * a.S + 1; i += BLOCK) s_eps[i] = a.eps[i];
+    for (int i = tid; i < stage_table_len(a.S); i += BLOCK) s_eps[i] = a.eps[i];
     __syncthreads();
     const int64_t idx = (int64_t)blockIdx.x * BLOCK + tid;
     if (idx >= a.B * a.ns) return;
@@ -239,7 +240,8 @@ __global__ void FES_LAUNCH_BOUNDS fes_shoot_kernel(const ShootArgs<T> a) {
         tr, [&](int c) { return __ldg(trow + c * a.tB); }, [&](int c) { return __ldg(crow + c * a.cB); }, a.N,
         a.tile_off, iv);
     for (int i = 0; i < a.S; ++i)
-        rk_step<T, KIND, FAT, GROUPS>(tr, iv, a.scheme, a.h, s_eps[2 * i], s_eps[2 * i + 1], s_eps[2 * i + 2], x, tg);
+        rk_step<T, KIND, FAT, GROUPS>(tr, iv, a.scheme, a.h, s_eps[2 * i], s_eps[2 * i + 1], s_eps[2 * i + 2],
+                                      s_eps + 2 * a.S + 1 + 4 * i, x, tg);
 
 #pragma unroll
     for (int j = 0; j < NX; ++j) {
@@ -260,7 +262,7 @@ __global__ void FES_LAUNCH_BOUNDS fes_shoot_kernel(const ShootArgs<T> a) {
 // ---------------------------------------------------------------------------------------------
 template <typename T>
 inline size_t ivp_smem_bytes(const IvpArgs<T> &a) {
-    size_t n = (2 * a.S + 1 + 3) & ~3;
+    size_t n = (stage_table_len(a.S) + 3) & ~3;
     if (a.tS == 0) n += (size_t)a.chunk * a.row;
     if (a.nu > 0 && a.cS == 0) n += (size_t)a.chunk * a.nu;
     return n * sizeof(T);
@@ -277,7 +279,7 @@ template <typename T, int KIND, bool FAT, int GROUPS>
 int launch_shoot_t(const ShootArgs<T> &a, cudaStream_t s) {
     const int64_t total = a.B * a.ns;
     const unsigned grid = (unsigned)((total + BLOCK - 1) / BLOCK);
-    const size_t smem = ((2 * a.S + 1 + 3) & ~3) * sizeof(T);
+    const size_t smem = ((stage_table_len(a.S) + 3) & ~3) * sizeof(T);
     fes_shoot_kernel<T, KIND, FAT, GROUPS><<<grid, BLOCK, smem, s>>>(a);
     return (int)cudaGetLastError();
 }

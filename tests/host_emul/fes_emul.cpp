@@ -25,7 +25,7 @@ void tables_cpu(const FesDesc *d, const double *win, const Carve &c, void *ws) {
     const double h = d->dt / S, tauc = d->tauc;
     const int64_t tB = c.tB;
     const int64_t wB = (d->flags & FES_WIN_SHARED) ? 1 : d->batch, wS = (d->flags & FES_WIN_SHARED) ? 0 : 1;
-    for (int i = 0; i < 2 * S + 1; ++i) eps[i] = (T)std::exp(-(0.5 * h * (double)i) / tauc);
+    for (int i = 0; i < stage_table_len(S); ++i) eps[i] = (T)stage_table_entry(i, S, h, tauc, d->scheme);
     for (int64_t node = 0; node < ns; ++node)
         for (int64_t b = 0; b < tB; ++b) {
             const double tn = d->t_start + d->dt * (double)node;
@@ -81,7 +81,8 @@ int ivp_cpu(const IvpArgs<T> &a) {
             interval_setup<T, KIND, FAT, GROUPS>(
                 tr, [&](int c) { return trow[c * a.tB]; }, [&](int c) { return crow[c * a.cB]; }, a.N, a.tile_off, iv, lcp);
             for (int i = 0; i < a.S; ++i) {
-                rk_step<T, KIND, FAT, GROUPS>(tr, iv, a.scheme, a.h, a.eps[2 * i], a.eps[2 * i + 1], a.eps[2 * i + 2], x, tg);
+                rk_step<T, KIND, FAT, GROUPS>(tr, iv, a.scheme, a.h, a.eps[2 * i], a.eps[2 * i + 1], a.eps[2 * i + 2],
+                                              a.eps + 2 * a.S + 1 + 4 * i, x, tg);
                 if (tr_on && a.trace_mode == 1) put_state((int64_t)node * a.S + i + 1);
             }
             if (tr_on) {
@@ -117,7 +118,8 @@ int shoot_cpu(const ShootArgs<T> &a) {
             interval_setup<T, KIND, FAT, GROUPS>(
                 tr, [&](int c) { return trow[c * a.tB]; }, [&](int c) { return crow[c * a.cB]; }, a.N, a.tile_off, iv);
             for (int i = 0; i < a.S; ++i)
-                rk_step<T, KIND, FAT, GROUPS>(tr, iv, a.scheme, a.h, a.eps[2 * i], a.eps[2 * i + 1], a.eps[2 * i + 2], x, tg);
+                rk_step<T, KIND, FAT, GROUPS>(tr, iv, a.scheme, a.h, a.eps[2 * i], a.eps[2 * i + 1], a.eps[2 * i + 2],
+                                              a.eps + 2 * a.S + 1 + 4 * i, x, tg);
             for (int j = 0; j < NX; ++j) {
                 if (a.Phi) a.Phi[(k * NX + j) * a.B + b] = x[j];
                 if (a.G) a.G[(k * NX + j) * a.B + b] = a.X[((k + 1) * NX + j) * a.B + b] - x[j];
