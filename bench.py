@@ -43,13 +43,13 @@ def flop_alg_per_step():
       nominal fatigue A, Tau1, Km reduced to the scalar Wn within the step (fes_core.cuh, rk_step_scheme):
                       Wn' 2 + Wn accumulate 2 + Wn stage 1 + 3 stage states x 2 FMA = 17 per middle stage,
                       14 first stage, 4 last stage, 12 to rebuild the three states                 =  64
-      shared modes    2 scalars x (3 stage FMAs + 4 update FMAs)                                  =  28
+      shared modes    mu, nu = step-start value x loop-invariant stage factor: 2 x (3 stages + 1 after the step) =   8
       reduced column  stage: 5 (vF row; 3 for the F0 column) + 2 (W row); update 2 x 7 FMA = 28
                       -> 56 x 4 columns + 48 (F0)                                                  = 272
-    Total 486 (the shipped SASS executes 513: the reciprocal's three Newton FMAs count as one flop here).  It is
+    Total 466 (the shipped SASS executes 491: the reciprocal's three Newton FMAs count as one flop here).  It is
     lower than SURVEY 8d's 978 because the fatigue block of every tangent column collapses to one scalar W
     (fes_core.cuh, dir_reduced) and Cn rides on the tabulated modes; the survey figure is reported beside it."""
-    return 96 + 12 + 14 + 64 + 28 + 272
+    return 96 + 12 + 14 + 64 + 8 + 272
 
 
 class ClockSampler(threading.Thread):

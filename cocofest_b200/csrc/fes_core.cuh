@@ -626,7 +626,11 @@ FES_HD void rk_step_scheme(const Traj<T> &tr, const Interval<T, Dirs<KIND, FAT, 
         const T ha = h * T(LAST ? 0.0 : TB::alpha(s + 1));
         const T eps = e[TB::eps_at(s)];
         T mu_s = T(0), nu_s = T(0);
-        if constexpr (MODES) {
+        if constexpr (MODES && sizeof(T) == 8) {
+            // the decaying scalars are the step-start values times the loop-invariant stage factors fm / dl
+            mu_s = s == 0 ? (T)tg.mu : (T)tg.mu * fm[s];
+            nu_s = s == 0 ? (T)tg.nu : (T)tg.nu * dl[s];
+        } else if constexpr (MODES) {  // f32 build: the stage factors would be floats, keep the double recurrences
             mu_s = (T)mus;
             nu_s = (T)nus;
             if constexpr (TB::beta(s) != 0.0) {
@@ -693,7 +697,10 @@ FES_HD void rk_step_scheme(const Traj<T> &tr, const Interval<T, Dirs<KIND, FAT, 
 #pragma unroll
         for (int j = (CNF && dir_forced_cn(C)) ? 1 : dir_first(FAT, C); j < dir_last(FAT, C); ++j) tg.V[d][j] = vn[d][j];
     });
-    if constexpr (MODES) {
+    if constexpr (MODES && sizeof(T) == 8) {
+        tg.mu *= (double)fm[NS];
+        tg.nu *= (double)dl[NS];
+    } else if constexpr (MODES) {
         tg.mu = mun;
         tg.nu = nun;
     }
