@@ -665,6 +665,58 @@ FES_HD void rk_step_scheme(const Traj<T> &tr, const Interval<T, Dirs<KIND, FAT, 
             }
         });
     };
+#ifdef FES_PROPAGATOR
+    constexpr bool PROP = !FAT && ND > 0 && SCHEME == 4;
+#else
+    constexpr bool PROP = false;
+#endif
+    if constexpr (PROP) {
+        // Two-state models: the F-row of EVERY column is the same scalar linear ODE v' = cF(t) v + g_d(t), so one RK4 step
+        // is  v_end = Phi v + sum_s W_s g_d(s)  with Phi, W_s functions of cF at the four stages only -- shared by all
+        // columns (what the scheme does to a linear row, written out once).  The Cn components come from the stage table.
+        Stage<T> sq[NS];
+        static_for<0, NS>([&](auto is) { nominal_stage(is, sq[decltype(is)::value]); });
+        const T h2 = h * T(0.5), h6 = h * T(1.0 / 6.0);
+        const T p1 = h2 * sq[1].cF, p2 = h2 * sq[2].cF, p3 = h * sq[3].cF;
+        const T A1 = sq[0].cF, A2 = xfma(p1, A1, sq[1].cF), A3 = xfma(p2, A2, sq[2].cF), A4 = xfma(p3, A3, sq[3].cF);
+        const T Phi = xfma(h6, xfma(T(2), A2 + A3, A1 + A4), T(1));
+        const T w2 = T(2) + p3, w1 = xfma(p2, w2, T(2)), w0 = xfma(p1, w1, T(1));
+        const T W[NS] = {h6 * w0, h6 * w1, h6 * w2, h6};
+        T WC[NS], WGsum = T(0);
+        static_for<0, NS>([&](auto is) {
+            constexpr int q = decltype(is)::value;
+            WC[q] = W[q] * sq[q].cCn;
+            WGsum = xfma(W[q], sq[q].cG, WGsum);
+        });
+        static_for<0, ND>([&](auto ic) {
+            constexpr int d = decltype(ic)::value;
+            constexpr int C = D::code(d);
+            T acc = Phi * tg.V[d][1];
+            if constexpr (dir_has_cn(C)) {
+                const T c = tg.V[d][0];
+                acc = xfma(WC[0], c, acc);
+                static_for<1, NS>([&](auto is) {
+                    constexpr int q = decltype(is)::value;
+                    T vcn = c * dl[q];
+                    if constexpr (dir_forced_cn(C)) vcn = xfma(iv.sE[d], ps[q - 1], vcn);
+                    acc = xfma(WC[q], vcn, acc);
+                });
+                tg.V[d][0] = dir_forced_cn(C) ? xfma(c, dl[NS], iv.sE[d] * ps[3]) : c * dl[NS];
+            }
+            static_for<0, NS>([&](auto is) {
+                constexpr int q = decltype(is)::value;
+                if constexpr (C == D_A_REST) acc = xfma(W[q], sq[q].cA, acc);
+                if constexpr (C == D_TAU1_REST) acc = xfma(W[q], sq[q].cT1, acc);
+                if constexpr (C == D_KM_REST) acc = xfma(W[q], sq[q].cKm, acc);
+                if constexpr (C == D_TAU2) acc = xfma(W[q], sq[q].cT2, acc);
+            });
+            if constexpr (dir_has_dg(C)) acc = xfma(WGsum, iv.dg[d], acc);
+            tg.V[d][1] = acc;
+        });
+        x[0] = xfma(x[0], dl[NS], iv.E * ps[3]);
+        x[1] = xn[1];
+        return;
+    }
 #ifdef FES_NOMINAL_AHEAD
     // experiment: issue the nominal chain of stage s+1 (which depends only on the nominal stage s) ahead of the
     // columns of stage s, so that its reciprocal chain overlaps their FMAs; two Stage records are live
