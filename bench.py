@@ -43,13 +43,16 @@ def flop_alg_per_step():
       nominal fatigue A, Tau1, Km reduced to the scalar Wn within the step (fes_core.cuh, rk_step_scheme):
                       Wn' 2 + Wn accumulate 2 + Wn stage 1 + 3 stage states x 2 FMA = 17 per middle stage,
                       14 first stage, 4 last stage, 12 to rebuild the three states                 =  64
-      shared modes    mu, nu = step-start value x loop-invariant stage factor: 2 x (3 stages + 1 after the step) =   8
-      reduced column  stage: 5 (vF row; 3 for the F0 column) + 2 (W row); update 2 x 7 FMA = 28
-                      -> 56 x 4 columns + 48 (F0)                                                  = 272
-    Total 466 (the shipped SASS executes 491: the reciprocal's three Newton FMAs count as one flop here).  It is
+      reduced columns advance through the shared 2 x 2 RK4 step propagator (fes_core.cuh, PROP2):
+                      Lambda_s / Phi recursion from cF, cW at the four stages (2+3+9+6+10+6+10, Phi sums 14)  =  60
+                      forcing weights S = sum_s p_s X_s: Cn0 profile 15, shared p_s m_s 5, A0 / Tau10 / Km0 12 each =  56
+                      columns: Phi v 6 x 5 + forcing 2 FMA x 2 components x 4                      =  46
+                      shared modes mu, nu: one multiply each after the step                        =   2
+    Total 350 (the shipped SASS executes 373: the reciprocal's three Newton FMAs count as one flop here).  It is
     lower than SURVEY 8d's 978 because the fatigue block of every tangent column collapses to one scalar W
-    (fes_core.cuh, dir_reduced) and Cn rides on the tabulated modes; the survey figure is reported beside it."""
-    return 96 + 12 + 14 + 64 + 8 + 272
+    (fes_core.cuh, dir_reduced), Cn rides on the tabulated modes and the (vF, W) rows of all columns share one
+    step propagator; the survey figure is reported beside it.  (Stage-by-stage columns, before PROP2: 466.)"""
+    return 96 + 12 + 14 + 64 + 60 + 56 + 46 + 2
 
 
 class ClockSampler(threading.Thread):

@@ -116,6 +116,24 @@ constexpr bool dirs_forced_cn() {
 // such a "reduced" column carries 2 or 3 numbers instead of 5.  The Cn0 column's own Cn component is the
 // second shared scalar (vCn' = -vCn/tauc), which leaves that column with (vF, W) as well.
 constexpr bool dir_reduced(bool fat, int c) { return fat && c <= D_WT; }
+template <class D>
+constexpr bool dirs_all_reduced() {
+    for (int d = 0; d < D::ND; ++d)
+        if (!dir_reduced(D::NX == 5, D::code(d))) return false;
+    return true;
+}
+template <class D>
+constexpr bool dirs_any_forced_cn() {
+    for (int d = 0; d < D::ND; ++d)
+        if (dir_forced_cn(D::code(d))) return true;
+    return false;
+}
+template <class D>
+constexpr bool dirs_have(int c) {
+    for (int d = 0; d < D::ND; ++d)
+        if (D::code(d) == c) return true;
+    return false;
+}
 // components stored in V[d][...] for a column of code c: [first, last)
 constexpr int dir_first(bool fat, int c) {
     if (dir_reduced(fat, c)) return (dir_has_cn(c) && c != D_CN0) ? 0 : 1;
@@ -715,6 +733,116 @@ FES_HD void rk_step_scheme(const Traj<T> &tr, const Interval<T, Dirs<KIND, FAT, 
         });
         x[0] = xfma(x[0], dl[NS], iv.E * ps[3]);
         x[1] = xn[1];
+        return;
+    }
+#ifndef FES_NO_PROP2  // measured against the stage-by-stage reduced columns (profiles/r01_tune_prop2_ag.txt): headline +15 %
+    constexpr bool PROP2 = FAT && ND > 0 && SCHEME == 4 && dirs_all_reduced<D>() &&
+                           (CNF || !dirs_any_forced_cn<D>());
+#else
+    constexpr bool PROP2 = false;
+#endif
+    if constexpr (PROP2) {
+        // Fatigue models, reduced columns: every column is the same 2 x 2 linear system
+        //     (vF, W)' = M(t) (vF, W) + g_d(t) e_F,    M = [[cF, cW], [1, -1/tau_fat]],
+        // so one RK4 step is  v_end = Phi v + sum_s (Lambda_s e_F) g_d(s),  Lambda_s = beta_s h I + a_{s+1} h Lambda_{s+1} M_{s+1}
+        // (the total weight of stage s in the step), Phi = I + sum_s Lambda_s M_s -- functions of cF, cW at the four stages
+        // only, written out once for all columns.  p_s = Lambda_s e_F, r_s = Lambda_s e_W; T_s1 = Lambda_s M_s e_F, T_s2 = Lambda_s M_s e_W.
+        Stage<T> sq[NS];
+        static_for<0, NS>([&](auto is) { nominal_stage(is, sq[decltype(is)::value]); });
+        const T h2 = h * T(0.5), h3 = h * T(1.0 / 3.0), h6 = h * T(1.0 / 6.0), kp = tr.kappa;
+        const T t41_0 = h6 * sq[3].cF, t41_1 = h6, t42_0 = h6 * sq[3].cW, t42_1 = -(kp * h6);
+        const T p3_0 = xfma(h, t41_0, h3), p3_1 = h * t41_1, r3_0 = h * t42_0, r3_1 = xfma(h, t42_1, h3);
+        const T t31_0 = xfma(p3_0, sq[2].cF, r3_0), t31_1 = xfma(p3_1, sq[2].cF, r3_1);
+        const T t32_0 = xfma(p3_0, sq[2].cW, -(kp * r3_0)), t32_1 = xfma(p3_1, sq[2].cW, -(kp * r3_1));
+        const T p2_0 = xfma(h2, t31_0, h3), p2_1 = h2 * t31_1, r2_0 = h2 * t32_0, r2_1 = xfma(h2, t32_1, h3);
+        const T t21_0 = xfma(p2_0, sq[1].cF, r2_0), t21_1 = xfma(p2_1, sq[1].cF, r2_1);
+        const T t22_0 = xfma(p2_0, sq[1].cW, -(kp * r2_0)), t22_1 = xfma(p2_1, sq[1].cW, -(kp * r2_1));
+        const T p1_0 = xfma(h2, t21_0, h6), p1_1 = h2 * t21_1, r1_0 = h2 * t22_0, r1_1 = xfma(h2, t22_1, h6);
+        const T t11_0 = xfma(p1_0, sq[0].cF, r1_0), t11_1 = xfma(p1_1, sq[0].cF, r1_1);
+        const T t12_0 = xfma(p1_0, sq[0].cW, -(kp * r1_0)), t12_1 = xfma(p1_1, sq[0].cW, -(kp * r1_1));
+        const T Phi00 = T(1) + ((t11_0 + t21_0) + (t31_0 + t41_0)), Phi10 = (t11_1 + t21_1) + (t31_1 + t41_1);
+        const T Phi01 = (t12_0 + t22_0) + (t32_0 + t42_0), Phi11 = T(1) + ((t12_1 + t22_1) + (t32_1 + t42_1));
+        const T pF[NS] = {p1_0, p2_0, p3_0, h6}, pW[NS] = {p1_1, p2_1, p3_1, T(0)};
+        // S(X) = sum_s p_s X_s for the forcing profiles the columns of this set use
+        auto wsum = [&](auto coef, T &sF, T &sW) {
+            const T c0 = coef(std::integral_constant<int, 0>{}), c1 = coef(std::integral_constant<int, 1>{});
+            const T c2 = coef(std::integral_constant<int, 2>{}), c3 = coef(std::integral_constant<int, 3>{});
+            sF = xfma(pF[3], c3, xfma(pF[2], c2, xfma(pF[1], c1, pF[0] * c0)));
+            sW = xfma(pW[2], c2, xfma(pW[1], c1, pW[0] * c0));
+        };
+        constexpr bool ANY_CN = dirs_have<D>(D_CN0) || dirs_any_forced_cn<D>();
+        T sCdF = T(0), sCdW = T(0), sCpF = T(0), sCpW = T(0), sAF = T(0), sAW = T(0), sT1F = T(0), sT1W = T(0);
+        T sKmF = T(0), sKmW = T(0), sGF = T(0), sGW = T(0);
+        if constexpr (ANY_CN)
+            wsum([&](auto q) { constexpr int s = decltype(q)::value; return s == 0 ? sq[0].cCn : sq[s].cCn * dl[s]; }, sCdF, sCdW);
+        if constexpr (dirs_any_forced_cn<D>()) {
+            sCpF = xfma(pF[3], sq[3].cCn * ps[2], xfma(pF[2], sq[2].cCn * ps[1], pF[1] * (sq[1].cCn * ps[0])));
+            sCpW = xfma(pW[2], sq[2].cCn * ps[1], pW[1] * (sq[1].cCn * ps[0]));
+        }
+        if constexpr (dirs_have<D>(D_A0) || dirs_have<D>(D_TAU10) || dirs_have<D>(D_KM0)) {
+            // the three fatigue-seed columns share the weights p_s m_s (m_s = the stage values of the decaying mode)
+            const T qF[NS] = {pF[0], pF[1] * fm[1], pF[2] * fm[2], pF[3] * fm[3]}, qW[NS] = {pW[0], pW[1] * fm[1], pW[2] * fm[2], T(0)};
+            auto msum = [&](auto coef, T &sF, T &sW) {
+                sF = xfma(qF[3], coef(3), xfma(qF[2], coef(2), xfma(qF[1], coef(1), qF[0] * coef(0))));
+                sW = xfma(qW[2], coef(2), xfma(qW[1], coef(1), qW[0] * coef(0)));
+            };
+            if constexpr (dirs_have<D>(D_A0)) msum([&](int s) { return sq[s].cA; }, sAF, sAW);
+            if constexpr (dirs_have<D>(D_TAU10)) msum([&](int s) { return sq[s].cT1; }, sT1F, sT1W);
+            if constexpr (dirs_have<D>(D_KM0)) msum([&](int s) { return sq[s].cKm; }, sKmF, sKmW);
+        }
+        if constexpr (dirs_have<D>(D_PW))
+            wsum([&](auto q) { return sq[decltype(q)::value].cG; }, sGF, sGW);
+        const T mu0 = (T)tg.mu, nu0 = (T)tg.nu;
+        static_for<0, ND>([&](auto ic) {
+            constexpr int d = decltype(ic)::value;
+            constexpr int C = D::code(d);
+            const T vF = tg.V[d][1], vW = tg.V[d][2];
+            T aF = xfma(Phi01, vW, Phi00 * vF), aW = xfma(Phi11, vW, Phi10 * vF);
+            if constexpr (C == D_CN0) {
+                aF = xfma(sCdF, nu0, aF);
+                aW = xfma(sCdW, nu0, aW);
+            }
+            if constexpr (dir_forced_cn(C)) {
+                const T c = tg.V[d][0];
+                aF = xfma(sCpF, iv.sE[d], xfma(sCdF, c, aF));
+                aW = xfma(sCpW, iv.sE[d], xfma(sCdW, c, aW));
+                tg.V[d][0] = xfma(c, dl[NS], iv.sE[d] * ps[3]);
+            }
+            if constexpr (C == D_A0) {
+                aF = xfma(sAF, mu0, aF);
+                aW = xfma(sAW, mu0, aW);
+            }
+            if constexpr (C == D_TAU10) {
+                aF = xfma(sT1F, mu0, aF);
+                aW = xfma(sT1W, mu0, aW);
+            }
+            if constexpr (C == D_KM0) {
+                aF = xfma(sKmF, mu0, aF);
+                aW = xfma(sKmW, mu0, aW);
+            }
+            if constexpr (dir_has_dg(C)) {
+                aF = xfma(sGF, iv.dg[d], aF);
+                aW = xfma(sGW, iv.dg[d], aW);
+            }
+            tg.V[d][1] = aF;
+            tg.V[d][2] = aW;
+        });
+        x[0] = xfma(x[0], dl[NS], iv.E * ps[3]);
+        x[1] = xn[1];
+        x[2] = xfma(tr.alpha_a, wn_n, xfma(dA, fm[NS], tr.a_rest));
+        x[3] = xfma(tr.alpha_tau1, wn_n, xfma(dT1, fm[NS], tr.tau1_rest));
+        x[4] = xfma(tr.alpha_km, wn_n, xfma(dKm, fm[NS], tr.km_rest));
+        if constexpr (MODES && sizeof(T) == 8) {
+            tg.mu *= (double)fm[NS];
+            tg.nu *= (double)dl[NS];
+        } else if constexpr (MODES) {  // f32 build: a float cannot hold 1 - h/tau_fat, the step factors are formed in double
+            auto step_factor = [](double z) {
+                const double f1 = fma(-0.5 * z, 1.0, 1.0), f2 = fma(-0.5 * z, f1, 1.0), f3 = fma(-z, f2, 1.0);
+                return fma(-z * (1.0 / 6.0), (1.0 + f3) + 2.0 * (f1 + f2), 1.0);
+            };
+            tg.mu *= step_factor(zf);
+            tg.nu *= step_factor(zc);
+        }
         return;
     }
 #ifdef FES_NOMINAL_AHEAD
