@@ -48,7 +48,7 @@ def flop_alg_per_step():
                       forcing weights S = sum_s p_s X_s: Cn0 profile 15, shared p_s m_s 5, A0 / Tau10 / Km0 12 each =  56
                       columns: Phi v 6 x 5 + forcing 2 FMA x 2 components x 4                      =  46
                       shared modes mu, nu: one multiply each after the step                        =   2
-    Total 350 (the shipped SASS executes 373: the reciprocal's three Newton FMAs count as one flop here).  It is
+    Total 350 (the shipped SASS executes 375: the reciprocal's three Newton FMAs count as one flop here).  It is
     lower than SURVEY 8d's 978 because the fatigue block of every tangent column collapses to one scalar W
     (fes_core.cuh, dir_reduced), Cn rides on the tabulated modes and the (vF, W) rows of all columns share one
     step propagator; the survey figure is reported beside it.  (Stage-by-stage columns, before PROP2: 466.)"""

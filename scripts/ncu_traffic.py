@@ -1,0 +1,44 @@
+#!/usr/bin/env python
+"""Merges the figures of one `ncu --set full` capture of the bench kernel into profiles/r01_ivp_x0_static.json
+(`ncu_full_capture`), which bench.py reads for `roofline.traffic`.
+Usage: ncu_traffic.py report.ncu-rep summary.tsv [batch] [final_time_s]"""
+import csv
+import io
+import json
+import subprocess
+import sys
+from pathlib import Path
+
+ROOT = Path(__file__).resolve().parent.parent
+OUT = ROOT / "profiles" / "r01_ivp_x0_static.json"
+rep, summary = sys.argv[1], sys.argv[2]
+batch = int(sys.argv[3]) if len(sys.argv) > 3 else 1 << 20
+final_time = int(sys.argv[4]) if len(sys.argv) > 4 else 300
+raw = subprocess.run(["ncu", "-i", rep, "--page", "raw", "--csv"], capture_output=True, text=True, check=True).stdout
+rows = list(csv.reader(io.StringIO(raw[raw.index('"ID"'):])))
+hdr, units, vals = rows[0], rows[1], rows[2]
+
+
+def get(name, scale=None):
+    i = hdr.index(name)
+    v = float(vals[i].replace(",", ""))
+    u = units[i].lower()
+    if scale == "bytes":
+        v *= {"byte": 1, "kbyte": 1e3, "mbyte": 1e6, "gbyte": 1e9, "tbyte": 1e12}[u]
+    if scale == "seconds":
+        v *= {"ns": 1e-9, "us": 1e-6, "ms": 1e-3, "s": 1.0, "second": 1.0, "nsecond": 1e-9, "usecond": 1e-6, "msecond": 1e-3}[u]
+    return v
+
+
+rd, wr = get("dram__bytes_read.sum", "bytes"), get("dram__bytes_write.sum", "bytes")
+d = json.loads(OUT.read_text()) if OUT.exists() else {}
+d["ncu_full_capture"] = {
+    "report": f"{rep} (summary: {summary})", "batch": batch, "final_time_s": final_time,
+    "dram_bytes_read": int(rd), "dram_bytes_write": int(wr), "dram_bytes": int(rd + wr),
+    "gpu_time_duration_s": get("gpu__time_duration.sum", "seconds"),
+    "fp64_pipe_active_pct": get("sm__pipe_fp64_cycles_active.avg.pct_of_peak_sustained_active"),
+    "registers": int(get("launch__registers_per_thread")),
+    "waves_per_sm": round(get("launch__waves_per_multiprocessor"), 2),
+}
+OUT.write_text(json.dumps(d, indent=1) + "\n")
+print(json.dumps(d["ncu_full_capture"]))
