@@ -17,9 +17,11 @@
 // therefore contains no exp at all; the two divisions of F' share one reciprocal (MUFU.RCP64H + 5 DFMA,
 // no slow path).  Sensitivities are the exact tangent of the discrete RK map (what casadi's forward AD of
 // the unrolled integrator yields): the nominal stages record the few non-trivial Jacobian entries of F'
-// and every direction column is then pushed through the same four stages; columns are independent, so
-// the compiler interleaves them for ILP.  Structural zeros (Cn decouples from every state, fatigue rows
-// are linear) are removed at compile time through the direction code of each column.
+// and every direction column is advanced with them -- for RK4 through a step propagator shared by all columns
+// (what the scheme does to the linear tangent rows, written out once per step: scalar for the two-state models,
+// 2 x 2 for the reduced fatigue columns; rk_step_scheme), otherwise stage by stage.  Structural zeros (Cn
+// decouples from every state, fatigue rows are linear) are removed at compile time through the direction
+// code of each column.
 #pragma once
 
 #include <stdint.h>
