@@ -84,3 +84,18 @@ def rel_err(a, b, floor=1e-12):
     a, b = np.asarray(a, dtype=np.float64), np.asarray(b, dtype=np.float64)
     scale = max(np.max(np.abs(b)), 1e-300)
     return float(np.max(np.abs(a - b) / np.maximum(np.abs(b), floor * scale + 1e-300)))
+
+
+def entry_err(got, ref, keep, tiny=1e-300):
+    """Strict relative error for blocks whose entries differ by orders of magnitude (sensitivity matrices): every
+    entry (the index along the axes `keep`, e.g. (state row, direction column)) is compared on ITS OWN scale, the
+    largest magnitude that entry takes over the remaining axes (batch, nodes).  An entry that is structurally zero in the
+    reference, or has decayed below `tiny` there, must be below `tiny` in `got` too.  Returns the worst entry's error."""
+    got, ref = np.asarray(got, dtype=np.float64), np.asarray(ref, dtype=np.float64)
+    assert got.shape == ref.shape, (got.shape, ref.shape)
+    keep = tuple(k % ref.ndim for k in keep)
+    red = tuple(a for a in range(ref.ndim) if a not in keep)
+    scale = np.max(np.abs(ref), axis=red)
+    diff = np.max(np.abs(got - ref), axis=red)
+    err = np.where(scale > tiny, diff / np.maximum(scale, tiny), np.where(diff <= tiny, 0.0, np.inf))
+    return float(np.max(err))

@@ -13,7 +13,7 @@ from cocofest_b200._lib import FesLibraryError
 from oracle import fes_oracle as fo
 from oracle import fes_oracle_ident as foi
 from tests.conftest import BACKENDS
-from tests.problems import rel_err
+from tests.problems import entry_err, rel_err
 
 KINDS = {"ding2003": fo.DING2003, "ding2007": fo.DING2007, "hmed2018": fo.HMED2018}
 # default boxes / initial guesses of the reference identification classes
@@ -67,10 +67,38 @@ def test_cost_gradient_hessian_match_oracle(backend, name, shared_target):
                        torch.tensor(target[0] if shared_target else target.T.copy(), device=backend), ctrl=_ctrl_tensor(pr, backend),
                        weight=torch.tensor(weight, device=backend), x0=torch.tensor(x0.T.copy(), device=backend), max_iter=0)
     assert rel_err(res.cost.cpu().numpy(), c) < 1e-9
-    assert rel_err(res.grad.cpu().numpy().T, g) < 1e-9
-    assert rel_err(np.transpose(res.hessian().cpu().numpy(), (2, 0, 1)), H) < 1e-9
+    assert entry_err(res.grad.cpu().numpy().T, g, keep=(1,)) < 1e-9                                   # per parameter
+    assert entry_err(np.transpose(res.hessian().cpu().numpy(), (2, 0, 1)), H, keep=(1, 2)) < 1e-9      # per (d, e) entry
     np.testing.assert_array_equal(res.params.cpu().numpy(), params.T)  # max_iter = 0 leaves the candidates alone
     assert (res.evaluations.cpu().numpy() == 1).all()
+
+
+@pytest.mark.parametrize("backend", BACKENDS, indirect=True)
+@pytest.mark.parametrize("name", list(KINDS))
+@pytest.mark.parametrize("shared_target", [True, False])
+def test_cost_gradient_hessian_fp32_mode(backend, name, shared_target):
+    """fes_identify_f32 against the fp64 oracle at north_star's 1e-4: cost per candidate, every gradient / Gauss-Newton
+    entry on its own scale."""
+    kind = KINDS[name]
+    pr = _protocol(kind, seed=1)
+    rng = np.random.default_rng(2)
+    B, ns = 9, pr["ns"]
+    params = fo.default_params(kind)[None] * rng.uniform(0.8, 1.25, (B, fo.NP_FULL))
+    F_true, _ = foi.node_forces(kind, fo.default_params(kind)[None], pr["win"][None], pr["u"], ns, 10, pr["dt"], pr["tauc"])
+    target = F_true if shared_target else F_true * rng.uniform(0.9, 1.1, (B, ns + 1))
+    weight = rng.uniform(0.5, 1.5, ns + 1) * pr["dt"]
+    x0 = np.stack([rng.uniform(0, 0.3, B), rng.uniform(0, 40, B)], axis=1)
+    c, g, H = foi.cost_grad_hess(kind, params, pr["win"][None], pr["u"], target, ns, 10, pr["dt"], pr["tauc"], weight=weight, x0=x0)
+    f32 = torch.float32
+    u = _ctrl_tensor(pr, backend)
+    res = fes.identify(kind, torch.tensor(params.T.copy(), dtype=f32, device=backend), torch.tensor(pr["win"], device=backend),
+                       pr["dt"], torch.tensor(target[0] if shared_target else target.T.copy(), dtype=f32, device=backend),
+                       ctrl=None if u is None else u.to(f32), weight=torch.tensor(weight, dtype=f32, device=backend),
+                       x0=torch.tensor(x0.T.copy(), dtype=f32, device=backend), max_iter=0, dtype=f32)
+    assert res.cost.dtype == f32
+    assert rel_err(res.cost.cpu().numpy(), c) < 1e-4
+    assert entry_err(res.grad.cpu().numpy().T, g, keep=(1,)) < 1e-4
+    assert entry_err(np.transpose(res.hessian().cpu().numpy(), (2, 0, 1)), H, keep=(1, 2)) < 1e-4
 
 
 @pytest.mark.parametrize("backend", BACKENDS, indirect=True)

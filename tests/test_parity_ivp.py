@@ -13,7 +13,7 @@ from cocofest_b200 import fes
 from oracle import fes_oracle as fo
 from oracle import fes_oracle_c as foc
 from tests.conftest import BACKENDS
-from tests.problems import MODELS, P_COLS, PF_COLS, oracle_win, random_problem, rel_err, to_lib
+from tests.problems import MODELS, P_COLS, PF_COLS, entry_err, oracle_win, random_problem, rel_err, to_lib
 
 GOLD = json.loads((Path(__file__).parent / "golden" / "ivp_golden.json").read_text())
 RTOL64 = 1e-9
@@ -105,9 +105,11 @@ def test_ivp_sensitivities_wrt_x0_match_oracle(backend, name):
                   pb["params"], pb["x0"], oracle_win(pb), pb["u"], seed_x0=True, trace_B=4, sens_trace=True)
     assert rel_err(res.x_final.cpu().numpy().T, ref["final"]) < RTOL64
     got = np.transpose(res.sens_final.cpu().numpy(), (2, 0, 1))  # [B, nx, nd]
-    assert rel_err(got, ref["sens_final"]) < RTOL64
+    # every (state row, direction column) entry on its own scale: the columns differ by orders of magnitude
+    assert entry_err(got, ref["sens_final"], keep=(1, 2)) < RTOL64
     got_t = np.transpose(res.sens_trace.cpu().numpy(), (3, 0, 1, 2))  # [tB, ns+1, nx, nd]
-    assert rel_err(got_t, ref["sens_trace"]) < RTOL64
+    assert entry_err(got_t[:, 1:], ref["sens_trace"][:, 1:], keep=(1, 2, 3)) < RTOL64   # per node as well
+    assert np.array_equal(got_t[:, 0], ref["sens_trace"][:, 0])                          # the seed is the identity
     assert len(res.columns) == pb["nx"]
 
 
@@ -129,22 +131,32 @@ def test_ivp_sensitivities_wrt_parameters_match_oracle(backend, name, with_pf):
     assert got.shape == ref["sens_final"].shape
     # column-wise relative error: columns differ by many orders of magnitude (d/dpd0 ~ 1e6, d/dalpha ~ 1e2)
     for c in range(got.shape[2]):
-        assert rel_err(got[:, :, c], ref["sens_final"][:, :, c]) < RTOL64, (name, res.columns[c])
+        assert entry_err(got[:, :, c], ref["sens_final"][:, :, c], keep=(1,)) < RTOL64, (name, res.columns[c])
 
 
 @pytest.mark.parametrize("backend", BACKENDS, indirect=True)
-@pytest.mark.parametrize("name", ["ding2003_with_fatigue", "ding2007", "hmed2018_with_fatigue"])
-def test_ivp_fp32_mode(backend, name):
-    pb = random_problem(name, B=16, seed=2)
+@pytest.mark.parametrize("name", list(MODELS))
+@pytest.mark.parametrize("group", ["x0", "p", "p|pf"])
+def test_ivp_fp32_mode(backend, name, group):
+    """north_star's fp32 mode: states AND sensitivities within 1e-4 of the fp64 oracle, every state on its own scale and
+    every (row, column) sensitivity entry on its own scale, for the six models and every IVP direction set."""
+    pb = random_problem(name, B=16, seed=2, shared_ctrl=False)
+    if group == "p|pf" and not pb["fat"]:
+        pytest.skip("fatigue parameters only exist on fatigue models")
+    dirs = {"x0": fes.FES_DIR_X0, "p": fes.FES_DIR_P, "p|pf": fes.FES_DIR_P | fes.FES_DIR_PF}[group]
     params, x0, win, ctrl = to_lib(pb, backend, dtype=torch.float32)
     res = fes.ivp(pb["kind"], pb["fat"], params, x0, win, pb["dt"], n_steps=10, ctrl=ctrl, n_shooting=pb["ns"],
-                  dirs=fes.FES_DIR_X0)
-    assert res.x_final.dtype == torch.float32
+                  dirs=dirs, trace="nodes", sens_trace=True)
+    assert res.x_final.dtype == torch.float32 and res.sens_final.dtype == torch.float32
+    kw = dict(seed_x0=True) if group == "x0" else dict(pdir=P_COLS[pb["kind"]] + (PF_COLS if group == "p|pf" else []))
     ref = foc.ivp(pb["kind"], pb["fat"], 4, pb["N"], pb["ns"], 10, pb["dt"], pb["tauc"], fo.R0_KM_RELATIONSHIP,
-                  pb["params"], pb["x0"], oracle_win(pb), pb["u"], seed_x0=True)
-    assert rel_err(res.x_final.cpu().numpy().T, ref["final"], floor=1e-3) < RTOL32
+                  pb["params"], pb["x0"], oracle_win(pb), pb["u"], trace_B=pb["B"], sens_trace=True, **kw)
+    assert entry_err(res.x_final.cpu().numpy().T, ref["final"], keep=(1,)) < RTOL32
+    assert entry_err(np.transpose(res.trace.cpu().numpy(), (2, 0, 1)), ref["trace"], keep=(2,)) < RTOL32
     got = np.transpose(res.sens_final.cpu().numpy(), (2, 0, 1))
-    assert rel_err(got, ref["sens_final"], floor=1e-3) < 20 * RTOL32
+    assert entry_err(got, ref["sens_final"], keep=(1, 2)) < RTOL32
+    got_t = np.transpose(res.sens_trace.cpu().numpy(), (3, 0, 1, 2))
+    assert entry_err(got_t[:, 1:], ref["sens_trace"][:, 1:], keep=(2, 3)) < RTOL32
 
 
 @pytest.mark.parametrize("backend", BACKENDS, indirect=True)
@@ -161,14 +173,22 @@ def test_ivp_long_fatigue_protocol_matches_oracle(backend):
     x0 = np.zeros((B, 5))
     x0[:, 2], x0[:, 3], x0[:, 4] = params[:, 0], params[:, 2], params[:, 1]
     res = fes.ivp(kind, fat, torch.tensor(params.T.copy(), device=backend), torch.tensor(x0.T.copy(), device=backend),
-                  torch.tensor(win, device=backend), T / ns, n_steps=10, n_shooting=ns, trace="nodes", dirs=fes.FES_DIR_X0)
-    ref = foc.ivp(kind, fat, 4, 10, ns, 10, T / ns, 0.020, 1.04, params, x0, win[None], None, seed_x0=True, trace_B=B)
+                  torch.tensor(win, device=backend), T / ns, n_steps=10, n_shooting=ns, trace="nodes", dirs=fes.FES_DIR_X0,
+                  sens_trace=True)
+    ref = foc.ivp(kind, fat, 4, 10, ns, 10, T / ns, 0.020, 1.04, params, x0, win[None], None, seed_x0=True, trace_B=B,
+                  sens_trace=True)
     got = np.transpose(res.trace.cpu().numpy(), (2, 0, 1))
     assert rel_err(got[:, :, 1], ref["trace"][:, :, 1], floor=1e-6) < RTOL64   # F at every node
-    assert rel_err(res.x_final.cpu().numpy().T, ref["final"]) < RTOL64
+    assert entry_err(res.x_final.cpu().numpy().T, ref["final"], keep=(1,)) < RTOL64
     gs = np.transpose(res.sens_final.cpu().numpy(), (2, 0, 1))
-    # sensitivities w.r.t. Cn0/F0 have decayed to ~1e-300 after 20 s: compare on the scale of the whole block
-    assert np.max(np.abs(gs - ref["sens_final"])) < RTOL64 * np.max(np.abs(ref["sens_final"]))
+    # every (row, column) entry on its own scale; after 20 s d Cn / d Cn0 has decayed below 1e-300 (it must have on both
+    # sides), so ALL entries are compared again at nodes where they are still representable
+    assert entry_err(gs, ref["sens_final"], keep=(1, 2), tiny=1e-200) < RTOL64
+    assert abs(ref["sens_final"][0, 0, 0]) < 1e-200 and np.min(np.abs(ref["sens_final"][:, 1:, :])) > 1e-12
+    st = np.transpose(res.sens_trace.cpu().numpy(), (3, 0, 1, 2))  # [B, ns+1, nx, nd]
+    for node in (1, 5, 33, 66):   # 30 ms .. 2 s: the Cn0 column has decayed by exp(-100) at most
+        assert np.min(np.max(np.abs(ref["sens_trace"][:, node, :, 0]), axis=0)) > 1e-60
+        assert entry_err(st[:, node], ref["sens_trace"][:, node], keep=(1, 2)) < RTOL64, node
 
 
 @pytest.mark.parametrize("backend", BACKENDS, indirect=True)
@@ -202,7 +222,7 @@ def test_ivp_edge_sizes(backend, name, B):
                   pb["params"], pb["x0"], oracle_win(pb), pb["u"], seed_x0=True)
     assert rel_err(res.x_final.cpu().numpy().T, ref["final"]) < RTOL64
     gs = np.transpose(res.sens_final.cpu().numpy(), (2, 0, 1))
-    assert np.max(np.abs(gs - ref["sens_final"])) < RTOL64 * np.max(np.abs(ref["sens_final"]))
+    assert entry_err(gs, ref["sens_final"], keep=(1, 2)) < RTOL64
     assert res.trace.shape == (pb["ns"] + 1, pb["nx"], B)
     from cocofest_b200._lib import FesLibraryError
     with pytest.raises(FesLibraryError):  # one past the limits

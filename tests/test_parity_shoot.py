@@ -8,9 +8,11 @@ from cocofest_b200 import fes
 from oracle import fes_oracle as fo
 from oracle import fes_oracle_c as foc
 from tests.conftest import BACKENDS
-from tests.problems import MODELS, P_COLS, PF_COLS, oracle_win, random_problem, rel_err, to_lib
+from tests.problems import MODELS, P_COLS, PF_COLS, entry_err, oracle_win, random_problem, rel_err, to_lib
 
 RTOL64 = 1e-9
+RTOL32 = 1e-4
+JKEEP = (2, 3)  # Jacobian blocks [B, ns, row, column]: every (row, column) entry on its own scale
 
 
 def _X(pb, seed=1):
@@ -52,18 +54,42 @@ def test_shoot_all_blocks_match_oracle(backend, name, scheme):
     Phi = np.transpose(res.Phi.cpu().numpy(), (2, 0, 1))
     assert rel_err(Phi, X[:, 1:] - ref["G"]) < RTOL64
     assert np.max(np.abs(G - ref["G"])) < RTOL64 * np.max(np.abs(Phi))
-    assert rel_err(_bl(res.Jx), ref["Jx"]) < RTOL64
+    assert entry_err(_bl(res.Jx), ref["Jx"], JKEEP) < RTOL64
     if pb["nu"]:
         assert res.Ju.shape[2] == pb["nu"]
-        assert rel_err(_bl(res.Ju), ref["Ju"]) < RTOL64
+        assert entry_err(_bl(res.Ju), ref["Ju"], JKEEP) < RTOL64
     else:
         assert res.Ju is None
     Jp = _bl(res.Jp)
     assert Jp.shape == ref["Jp"].shape
-    for c in range(Jp.shape[3]):
-        assert rel_err(Jp[..., c], ref["Jp"][..., c]) < RTOL64, (name, res.p_columns[c])
+    assert entry_err(Jp, ref["Jp"], JKEEP) < RTOL64, (name, res.p_columns)
     assert res.Jw.shape[2] == pb["N"]
-    assert rel_err(_bl(res.Jw), ref["Jw"], floor=1e-9) < 10 * RTOL64
+    assert entry_err(_bl(res.Jw), ref["Jw"], JKEEP) < RTOL64   # pulse-time block: same bar as the others
+
+
+@pytest.mark.parametrize("backend", BACKENDS, indirect=True)
+@pytest.mark.parametrize("name", list(MODELS))
+def test_shoot_fp32_mode(backend, name):
+    """fes_shoot_f32 against the fp64 oracle at north_star's 1e-4: end points per state, every Jacobian entry on its own scale."""
+    pb = random_problem(name, B=9, N=7, ns=8, seed=21, shared_ctrl=False)
+    S = 10
+    X = _X(pb)
+    params, _, win, ctrl = to_lib(pb, backend, dtype=torch.float32)
+    Xl = torch.tensor(np.ascontiguousarray(np.transpose(X, (1, 2, 0))), dtype=torch.float32, device=backend)
+    X32 = np.transpose(Xl.cpu().numpy().astype(np.float64), (2, 0, 1))   # the oracle starts from the same rounded nodes
+    want = ["x", "u", "p", "w"] + (["pf"] if pb["fat"] else [])
+    res = fes.shoot(pb["kind"], pb["fat"], params, Xl, win, pb["dt"], n_steps=S, ctrl=ctrl, want=want, endpoints=True)
+    assert res.Phi.dtype == torch.float32 and res.Jx.dtype == torch.float32
+    pdir = P_COLS[pb["kind"]] + (PF_COLS if pb["fat"] else [])
+    ref = foc.shoot(pb["kind"], pb["fat"], 4, pb["N"], pb["ns"], S, pb["dt"], 0.0, pb["tauc"], fo.R0_KM_RELATIONSHIP,
+                    pb["params"], X32, oracle_win(pb), pb["u"], pdir=pdir, want_x=True, want_u=pb["nu"] > 0, want_w=True)
+    Phi = np.transpose(res.Phi.cpu().numpy(), (2, 0, 1))
+    assert entry_err(Phi, X32[:, 1:] - ref["G"], keep=(2,)) < RTOL32
+    G = np.transpose(res.G.cpu().numpy(), (2, 0, 1))
+    assert np.max(np.abs(G - ref["G"]) / np.max(np.abs(Phi), axis=(0, 1))) < RTOL32   # a defect is a difference of states
+    for key, J in (("Jx", res.Jx), ("Ju", res.Ju), ("Jp", res.Jp), ("Jw", res.Jw)):
+        if J is not None:
+            assert entry_err(_bl(J), ref[key], JKEEP) < RTOL32, key
 
 
 @pytest.mark.parametrize("backend", BACKENDS, indirect=True)
@@ -84,7 +110,7 @@ def test_shoot_defects_only_and_shared_inputs(backend, name):
         res_u = fes.shoot(pb["kind"], pb["fat"], params, Xl, win, pb["dt"], n_steps=10, ctrl=ctrl, want=("u",))
         ref_u = foc.shoot(pb["kind"], pb["fat"], 4, pb["N"], pb["ns"], 10, pb["dt"], 0.0, pb["tauc"], fo.R0_KM_RELATIONSHIP,
                           pb["params"], X, oracle_win(pb), pb["u"], want_x=False, want_u=True)
-        assert rel_err(_bl(res_u.Ju), ref_u["Ju"]) < RTOL64
+        assert entry_err(_bl(res_u.Ju), ref_u["Ju"], JKEEP) < RTOL64
 
 
 @pytest.mark.parametrize("backend", BACKENDS, indirect=True)
@@ -96,9 +122,9 @@ def test_shoot_per_trajectory_windows(backend):
     res = fes.shoot(pb["kind"], pb["fat"], params, Xl, win, pb["dt"], n_steps=3, ctrl=ctrl, want=("x", "u", "w"))
     ref = foc.shoot(pb["kind"], pb["fat"], 4, pb["N"], pb["ns"], 3, pb["dt"], 0.0, pb["tauc"], fo.R0_KM_RELATIONSHIP,
                     pb["params"], X, oracle_win(pb), pb["u"], want_x=True, want_u=True, want_w=True)
-    assert rel_err(_bl(res.Jx), ref["Jx"]) < RTOL64
-    assert rel_err(_bl(res.Ju), ref["Ju"]) < RTOL64
-    assert rel_err(_bl(res.Jw), ref["Jw"], floor=1e-9) < 10 * RTOL64
+    assert entry_err(_bl(res.Jx), ref["Jx"], JKEEP) < RTOL64
+    assert entry_err(_bl(res.Ju), ref["Ju"], JKEEP) < RTOL64
+    assert entry_err(_bl(res.Jw), ref["Jw"], JKEEP) < RTOL64
 
 
 @pytest.mark.parametrize("backend", BACKENDS, indirect=True)
@@ -114,4 +140,6 @@ def test_chained_shoot_jacobians_equal_ivp_sensitivities(backend):
     M = torch.eye(pb["nx"], dtype=torch.float64, device=backend)[:, :, None].repeat(1, 1, pb["B"])
     for k in range(pb["ns"]):
         M = torch.einsum("ijb,jkb->ikb", sh.Jx[k], M)
-    assert torch.max(torch.abs(M - iv.sens_final)) < 1e-9 * torch.max(torch.abs(iv.sens_final))
+    scale = iv.sens_final.abs().amax(dim=2, keepdim=True)   # every (row, column) entry on its own scale
+    assert bool((M[scale.expand_as(M) == 0] == 0).all())     # structural zeros (d Cn / d anything but Cn0) stay zero
+    assert float(((M - iv.sens_final).abs() / scale.clamp_min(1e-300)).max()) < 1e-9
