@@ -9,7 +9,11 @@ Metric: trajectory-steps/s (one trajectory-step = one RK4 step of one trajectory
     python bench.py [--gpus N] [--steps K] [--warmup W] [--batch B] [--final-time T] [--impl reference]
 
 N > 1 is launched by torchrun (one rank per GPU, weak scaling: every rank integrates its own B trajectories,
-no data-path collective; results are all-gathered over NCCL inside the timed region).
+no data-path collective; results are all-gathered over NCCL inside the timed region).  The same line also carries
+  "strong"   (N > 1) the SAME B trajectories split over the N ranks, timed the same way;
+  "configs"  (N = 1) device-timed sub-records of BASELINE configs 1, 3, 4, 4c, 5 and of the headline workload in fp32,
+             with roofline fractions from the instruction counts of the shipped SASS (scripts/bench_configs.py);
+  "e2e.breakdown_ms"  the phases of the host-buffer call (allocation, H2D, kernels, D2H) as the library measured them.
 """
 import argparse
 import json
@@ -116,12 +120,15 @@ def physical_gpu_index(local_index):
 # ---------------------------------------------------------------------------------------------------------
 def cpu_reference_rate(proto, n_traj, n_intervals, threads, repeat=1):
     """Times the C restatement of the reference formulation (oracle/fes_oracle.c: N-term exp sum per RHS,
-    dual-number tangents = casadi forward AD) on `threads` host cores.  Returns (steps/s, seconds)."""
+    dual-number tangents = casadi forward AD) on `threads` host cores, in its TIMED build (-O3 -march=native, compiled
+    here, on the machine that runs the benchmark; the strict -ffp-contract=off build stays the parity oracle).
+    Returns (steps/s, seconds)."""
     import numpy as np
 
     from cocofest_b200 import protocols
     from oracle import fes_oracle_c as foc
 
+    cdll, _ = foc.timed_lib()
     params, x0 = protocols.fatigue_population(n_traj)
     p, x = params.numpy().T.copy(), x0.numpy().T.copy()
     win = np.ascontiguousarray(proto["win"][: n_intervals + 1])[None]
@@ -129,10 +136,54 @@ def cpu_reference_rate(proto, n_traj, n_intervals, threads, repeat=1):
     for _ in range(repeat):
         t0 = time.perf_counter()
         foc.ivp(0, True, 4, proto["N"], n_intervals, 10, proto["dt"], 0.020, 1.04, p, x, win, None, seed_x0=True,
-                n_threads=threads)
+                n_threads=threads, cdll=cdll)
         el = time.perf_counter() - t0
         best = el if best is None else min(best, el)
     return n_traj * n_intervals * 10 / best, best
+
+
+def cpu_hoisted_rate(proto, n_traj, n_intervals, threads):
+    """The KERNEL's own formulation (hoisted pulse sum, reduced tangents, step propagator) on the host cores: the kernel
+    source cocofest_b200/csrc/fes_core.cuh compiled by g++ (tests/host_emul/fes_emul.cpp, -O3 -march=native -fopenmp,
+    built here) and driven by a loop over trajectories.  Beside the reference-formulation port it separates what the
+    formulation buys from what the hardware buys.  Returns (steps/s, seconds, flags)."""
+    import ctypes
+    import subprocess
+
+    import numpy as np
+
+    from cocofest_b200 import _lib, fes, protocols
+
+    src = ROOT / "tests" / "host_emul"
+    out = src / "_timed"
+    out.mkdir(exist_ok=True)
+    so = out / "libfes_emul_timed.so"
+    flags = ["-O3", "-march=native", "-fopenmp", "-std=c++17", "-fPIC", "-Wno-unknown-pragmas"]
+    cxx = "/usr/bin/g++" if os.path.exists("/usr/bin/g++") else "g++"
+    subprocess.run([cxx, *flags, f"-I{ROOT / 'include'}", f"-I{ROOT / 'cocofest_b200' / 'csrc'}", "-shared", "-o", str(so),
+                    str(src / "fes_emul.cpp"), "-lm"], check=True)
+    emul = _lib._bind(ctypes.CDLL(str(so)))
+    try:
+        ctypes.CDLL("libgomp.so.1").omp_set_num_threads(int(threads))   # torchrun exports OMP_NUM_THREADS=1
+    except OSError:
+        pass
+    params, x0 = protocols.fatigue_population(n_traj)
+    p, x = np.ascontiguousarray(params.numpy()), np.ascontiguousarray(x0.numpy())   # [14, B], [5, B]: the library's layout
+    win = np.ascontiguousarray(proto["win"][: n_intervals + 1])
+    xf, sf = np.empty((5, n_traj)), np.empty((5, 5, n_traj))
+    desc = fes._desc(fes.FES_DING2003, True, 4, proto["N"], n_intervals, 10, fes.FES_DIR_X0, fes.FES_WIN_SHARED, n_traj,
+                     proto["dt"], 0.0, None, fes.R0_KM_RELATIONSHIP)
+    ptr = lambda a: ctypes.c_void_p(a.ctypes.data)
+    buf = fes.FesIvpBuffers(ptr(p), ptr(x), ptr(win), None, ptr(xf), None, ptr(sf), None, None, 0)
+    best = None
+    for _ in range(2):
+        t0 = time.perf_counter()
+        rc = emul.fes_ivp_host_f64(ctypes.byref(desc), ctypes.byref(buf), None)
+        el = time.perf_counter() - t0
+        if rc != 0:
+            raise RuntimeError(f"host build of the kernel source returned {rc}")
+        best = el if best is None else min(best, el)
+    return n_traj * n_intervals * 10 / best, best, " ".join(flags)
 
 
 def host_threads():
@@ -146,7 +197,7 @@ def host_threads():
 
 def size_cpu_sample(proto, threads, target_s):
     """Picks (trajectories, intervals) of the same workload worth about target_s seconds of CPU work."""
-    n0, k0 = 2 * max(threads, 1), min(proto["ns"], 132)
+    n0, k0 = 8 * max(threads, 1), min(proto["ns"], 330)   # large enough that thread start-up does not set the rate
     rate, _ = cpu_reference_rate(proto, n0, k0, threads, repeat=2)
     steps = rate * target_s
     n_int = min(proto["ns"], 660)            # first 20 s of the protocol
@@ -172,12 +223,15 @@ def run_reference(args):
         cpu_reference_rate(proto, n_traj, n_int, threads)
     el = time.perf_counter() - t0
     value = args.steps * n_traj * n_int * 10 / el
-    sample = f"{n_traj} trajectories x first {n_int} intervals ({n_int * 10} RK4 steps) of the workload per step"
+    sample = (f"a SAMPLE of the workload named in config: {n_traj} trajectories x the first {n_int} intervals ({n_int * 10} RK4 "
+              f"steps) per step, reference formulation with d x/d x0, timed build ({foc.timed_lib()[1]})")
+    cfg = workload_config(args, proto)
+    cfg["reference_arm_sample"] = sample
     line = {
         "impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
         "warmup": args.warmup, "ms_per_step": 1e3 * el / args.steps, "higher_is_better": True, "scaling": "weak",
         "vs_baseline": None, "dtype": "f64", "data": "synthetic",
-        "config": workload_config(args, proto),
+        "config": cfg,
         "cpu_baseline": {"value": value, "unit": UNIT, "cores": threads, "kind": "port", "sample": sample},
         "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
@@ -208,6 +262,8 @@ def main():
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--no-configs", action="store_true", help="skip the sub-records of the other BASELINE configurations")
+    ap.add_argument("--no-strong", action="store_true", help="skip the strong-scaling sub-record (N > 1)")
     ap.add_argument("--dtype", default="f64", choices=["f64", "f32"],
                     help="arithmetic type of the path (f32 = north_star's 1e-4 mode, reported against the FFMA rate)")
     args = ap.parse_args()
@@ -221,6 +277,7 @@ def main():
     import torch.distributed as dist
 
     from cocofest_b200 import _lib, fes, protocols, sharding
+    from scripts import bench_configs as bc
 
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
@@ -246,11 +303,14 @@ def main():
     flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)
     units_per_step = B * ns * S
 
+    def integrate(p, x, tB):
+        return fes.ivp(fes.FES_DING2003, True, p, x, win_d, proto["dt"], n_steps=S, n_shooting=ns,
+                       dirs=fes.FES_DIR_X0, trace="nodes", trace_batch=tB)
+
     def device_step():
-        res = fes.ivp(fes.FES_DING2003, True, params_d, x0_d, win_d, proto["dt"], n_steps=S, n_shooting=ns,
-                      dirs=fes.FES_DIR_X0, trace="nodes", trace_batch=trace_B)
+        res = integrate(params_d, x0_d, trace_B)
         if world > 1:
-            full = sharding.gather_last(torch.cat([res.x_final[:, None], res.sens_final], dim=1))
+            full = sharding.gather_last(torch.cat([res.x_final[:, None], res.sens_final], dim=1), batch=B * world)
             return res, full
         return res, None
 
@@ -260,10 +320,16 @@ def main():
             dist.barrier()
         torch.cuda.synchronize()
 
+    def max_over_ranks(x):
+        t = torch.tensor([x], dtype=torch.float64, device=dev)
+        if world > 1:
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.item())
+
     for _ in range(args.warmup):
         device_step()
         flush.fill_(1)
-    fp64_peak = fes.probe_fma_peak(f32, launches=5, device=dev)  # FFMA rate in f32 mode
+    fma_probe = fes.probe_fma_peak(f32, launches=5, device=dev)  # FFMA rate in f32 mode
 
     # ---- kernel arm: inputs resident in HBM ----------------------------------------------------------------
     sampler = ClockSampler(physical_gpu_index(local))
@@ -283,13 +349,48 @@ def main():
     barrier()
     clocks = sampler.stop()
     launches = L.fes_launch_count() - launches0
-    elapsed_ms = t_start.elapsed_time(t_end)
     kern_ms = [a.elapsed_time(b) for a, b in ev]  # ivp kernel (+ its tiny table kernel, + gather at N > 1)
-    t = torch.tensor([elapsed_ms], dtype=torch.float64, device=dev)
-    if world > 1:
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-    elapsed_ms = float(t.item())
+    elapsed_ms = max_over_ranks(t_start.elapsed_time(t_end))
     value = world * units_per_step * args.steps / (elapsed_ms * 1e-3)
+
+    # ---- strong scaling: the SAME B trajectories split over the N ranks (BASELINE configs[1]: "1M ... on 1-8 x B200") ----
+    strong = None
+    if world > 1 and not args.no_strong:
+        lo, hi = sharding.shard_bounds(B, rank, world)
+        # every rank takes its contiguous block of rank 0's population (same seeds on every rank)
+        ps_h, xs_h = protocols.fatigue_population(B, offset=0)
+        ps_d, xs_d = ps_h[:, lo:hi].to(tdt).to(dev).contiguous(), xs_h[:, lo:hi].to(tdt).to(dev).contiguous()
+        tB_s = max(0, min(trace_B, hi) - min(trace_B, lo))   # the first 1024 trajectories of the batch, wherever they live
+
+        def strong_step():
+            r = integrate(ps_d, xs_d, tB_s)
+            return sharding.gather_last(torch.cat([r.x_final[:, None], r.sens_final], dim=1), batch=B)
+
+        n_strong = max(args.steps, 4)
+        for _ in range(args.warmup):
+            strong_step()
+            flush.fill_(1)
+        barrier()
+        s0, s1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        s0.record()
+        for k in range(n_strong):
+            full = strong_step()
+            flush.fill_(k)
+        s1.record()
+        barrier()
+        strong_ms = max_over_ranks(s0.elapsed_time(s1)) / n_strong
+        strong_value = units_per_step / (strong_ms * 1e-3)
+        # resident blocks of the launch: 64 threads per block, as many blocks per SM as the register file holds
+        strong = {
+            "value": strong_value, "unit": UNIT, "ms_per_step": strong_ms, "steps": n_strong, "batch_total": B,
+            "batch_per_gpu": hi - lo, "scaling": "strong",
+            "efficiency_vs_this_runs_weak_rate": strong_value / value,
+            "note": "same 2^20-trajectory job split over the ranks; results all-gathered to every rank inside the timed "
+                    "region; efficiency = strong rate / the weak rate measured above on the same GPUs (per-GPU work is 1/N, "
+                    "so the last wave of resident blocks is the limiter, not NCCL)",
+            "checksum_force_mean": float(full[1, 0].mean().item()),
+        }
+        del ps_d, xs_d, full
 
     # ---- end-to-end arm: public API with HOST buffers (H2D + kernels + D2H inside the timed region) -----
     e2e = None
@@ -300,61 +401,100 @@ def main():
             return r
 
         r = None
-        for _ in range(2):  # allocates the pinned result buffers once and warms the stream-ordered device pool
+        for _ in range(2):  # allocates the pinned result buffers once and fills the library's staging pool
             r = e2e_step(r)
         barrier()
+        phases = []
         t0 = time.perf_counter()
         for _ in range(args.steps):
             r = e2e_step(r)  # results land in the same pinned host buffers, as a solver loop would keep them
+            phases.append(fes.last_host_timing())
         torch.cuda.synchronize()
-        el = time.perf_counter() - t0
-        t = torch.tensor([el], dtype=torch.float64, device=dev)
-        if world > 1:
-            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        el = max_over_ranks(time.perf_counter() - t0)
         h2d = params_h.numel() * esz + x0_h.numel() * esz + ns * proto["N"] * 8
         d2h = (r.x_final.numel() + r.sens_final.numel() + r.trace.numel()) * esz
-        e2e = {"value": world * units_per_step * args.steps / float(t.item()), "unit": UNIT,
+        mean = lambda k: statistics.mean(ph[k] for ph in phases)
+        e2e = {"value": world * units_per_step * args.steps / el, "unit": UNIT,
                "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
+               "ratio_to_device_value": world * units_per_step * args.steps / el / value,
+               "breakdown_ms": {"staging_alloc": mean("alloc_ms"), "h2d": mean("h2d_ms"), "kernels": mean("kernels_ms"),
+                                "d2h": mean("d2h_ms"), "call_total": mean("total_ms"),
+                                "wall_per_step": 1e3 * el / args.steps,
+                                "note": "rank 0's phases as measured inside the library (fes_last_host_timing: CUDA events on "
+                                        "the call's stream, host clock for allocation and total); staging memory comes from a "
+                                        "library-owned pool that stays mapped between calls"},
                "api": f"cocofest_b200.fes.ivp on pinned host tensors -> fes_ivp_host_{args.dtype} (C ABI)"}
 
-    # ---- roofline of the dominant kernel (fes_ivp_kernel<double, ding2003, fatigue, X0>) -----------------
+    # ---- roofline of the dominant kernel (fes_ivp_kernel<T, ding2003, fatigue, X0>) -----------------------
     flop = flop_alg_per_step()
     kernel_s = statistics.mean(kern_ms) * 1e-3
     achieved = flop * units_per_step / kernel_s / 1e12
-    static = {}
-    try:  # static SASS count of the RK4 path + dram traffic of one ncu --set full capture (scripts/sass_count.py, profiles/)
-        static = json.loads((ROOT / "profiles" / "r01_ivp_x0_static.json").read_text())
+    counts, counts_src = bc.load_sass_counts()
+    kname = bc.kernel_name("ivp", args.dtype, fes.FES_DING2003, True, fes.FES_DIR_X0)
+    kc = counts.get(kname) if counts else None
+    nominal = bc.nominal_peaks(dev, clocks["sm_max_mhz"])           # at the maximum SM clock: the larger denominator
+    nominal_run = bc.nominal_peaks(dev, clocks["sm_mhz"]) if clocks.get("sm_mhz") else nominal   # at the clock this run held
+    peak_nominal = nominal["fp32_tflops" if f32 else "fp64_tflops"]
+    peak = max(peak_nominal, fma_probe)
+    traffic, traffic_src = None, "no ncu --set full capture of this build and workload under profiles/"
+    try:  # dram bytes of one ncu --set full capture (scripts/ncu_traffic.py), valid only for the build it was taken from
+        cap = json.loads((ROOT / "profiles" / "r02_ivp_x0_traffic.json").read_text())
+        if cap.get("dtype", "f64") == args.dtype and cap.get("batch") == B and cap.get("final_time_s") == args.final_time:
+            if counts and cap.get("lib_sha256") == json.loads((_lib.LIB_PATH.parent / "sass_counts.json").read_text())["lib_sha256"]:
+                traffic, traffic_src = cap.get("dram_bytes"), "profiles/r02_ivp_x0_traffic.json (ncu --set full, same library sha256)"
+            else:
+                traffic_src = "profiles/r02_ivp_x0_traffic.json was captured from another build of the library: dropped"
     except Exception:
         pass
-    inst = None if f32 else static.get("fp64_inst_per_rk4_step")  # the SASS count is of the fp64 kernel
-    traffic = None
-    cap = static.get("ncu_full_capture", {})
-    if not f32 and cap.get("batch") == B and cap.get("final_time_s") == args.final_time:
-        traffic = cap.get("dram_bytes")
     hbm_bytes = (params_d.numel() + 2 * x0_d.numel() + 25 * B + (ns + 1) * 5 * trace_B) * esz
     peaks = {}
     try:
         peaks = json.loads((ROOT / "MEASURED_PEAKS.json").read_text())
     except Exception:
         pass
+    pipe = None
+    if kc:
+        inst = kc["fp32_inst" if f32 else "fp64_inst"]
+        rate = inst * units_per_step / kernel_s
+        pipe = {"inst_per_trajectory_step": inst, "flop_executed_per_trajectory_step": kc["fp32_flop" if f32 else "fp64_flop"],
+                "issue_rate_ginst_s": rate / 1e9,
+                "peak_ginst_s_nominal": nominal["fp32_inst_s" if f32 else "fp64_inst_s"] / 1e9,
+                "frac_of_nominal": rate / nominal["fp32_inst_s" if f32 else "fp64_inst_s"],
+                "frac_of_nominal_at_run_clock": rate / nominal_run["fp32_inst_s" if f32 else "fp64_inst_s"],
+                "frac_of_probe": rate / (fma_probe * 1e12 / 2) if fma_probe else None,
+                "registers": kc.get("registers"), "stack_bytes": kc.get("stack_bytes"),
+                "note": "FMA + MUL + ADD of the RK4 path counted in the shipped SASS; every one holds an issue slot of the pipe"}
     roofline = {
-        "bound": "fp32" if f32 else "fp64", "achieved": achieved, "peak": fp64_peak, "unit": "TFLOP/s", "frac": achieved / fp64_peak if fp64_peak else None,
-        "traffic": traffic,
-        "kernel": f"fes_ivp_kernel<{'float' if f32 else 'double'}, DING2003, fatigue, X0>", "kernel_ms": statistics.mean(kern_ms),
+        "bound": "fp32" if f32 else "fp64", "achieved": achieved, "peak": peak, "unit": "TFLOP/s", "frac": achieved / peak if peak else None,
+        "traffic": traffic, "traffic_source": traffic_src,
+        "kernel": kname, "kernel_ms": statistics.mean(kern_ms),
         "flop_alg_per_trajectory_step": flop,
+        "peaks": {"nominal_tflops": peak_nominal, "nominal_is": f"{nominal['sms']} SMs x {128 if f32 else 64} lanes x 2 x "
+                  f"{nominal['sm_mhz']} MHz (ncu's pipe peak x 2 flop)", "probe_tflops": fma_probe,
+                  "frac_vs_nominal": achieved / peak_nominal, "frac_vs_probe": achieved / fma_probe if fma_probe else None,
+                  "used": "nominal" if peak_nominal >= fma_probe else "probe"},
+        "pipe": pipe, "static_counts_source": counts_src,
         "survey_dense_formulation": {"flop_per_trajectory_step": flop_survey_per_step(5, 5),
-                                     "equivalent_tflops": flop_survey_per_step(5, 5) * units_per_step / kernel_s / 1e12,
-                                     "note": "SURVEY 8d counts the dense 5-component tangent; the kernel propagates the "
-                                             "exact same tangent through 2 components per column"},
-        "fp64_pipe": None if not inst else {
-            "inst_per_trajectory_step": inst, "issue_rate_ginst_s": inst * units_per_step / kernel_s / 1e9,
-            "peak_ginst_s": fp64_peak * 1e3 / 2, "frac": inst * units_per_step / kernel_s / 1e9 / (fp64_peak * 1e3 / 2),
-            "note": "DFMA+DMUL+DADD of the RK4 path counted in the shipped SASS; every one occupies a DFMA issue slot"},
-        "peak_source": ("FFMA" if f32 else "DFMA") + " probe (fes_probe_fma_peak) measured in this run on this GPU; "
-                       "MEASURED_PEAKS.json holds no fp64 / fp32 figure",
+                                     "note": "SURVEY 8d counts the dense 5-component tangent; the kernel propagates the exact "
+                                             "same tangent through 2 components per column and does not execute that count"},
+        "peak_source": "the LARGER of the nominal pipe rate at the maximum SM clock and the " + ("FFMA" if f32 else "DFMA")
+                       + " probe (fes_probe_fma_peak) of this run; MEASURED_PEAKS.json holds no fp64 / fp32 figure",
         "hbm": {"algorithmic_bytes": hbm_bytes, "achieved_gbs": hbm_bytes / kernel_s / 1e9, "peak_gbs": peaks.get("hbm_gbs"),
                 "note": "state, parameters and tangents stay in registers: HBM is idle by design"},
     }
+
+    # ---- the other BASELINE configurations and the fp32 mode, device-timed (rank 0, N = 1 only) ------------
+    configs, configs_meta = None, None
+    if world == 1 and not args.no_configs:
+        del params_d, x0_d
+        torch.cuda.empty_cache()
+        wanted = ["1", "3", "4", "4c", "5", "5pf"]
+        configs, configs_meta = bc.run_configs(wanted, dev, "f64", steps=3, warmup=3, flush=flush)
+        other = "f32" if not f32 else "f64"   # the headline workload in the other arithmetic type
+        r2, _ = bc.run_configs(["2x0"], dev, other, steps=2, warmup=2, flush=flush, t2=args.final_time)
+        configs += r2
+        r32, _ = bc.run_configs(["3", "4c", "5"], dev, "f32", steps=3, warmup=3, flush=flush)
+        configs += r32
 
     # ---- CPU baseline: the oracle's reference-formulation port on the host cores (rank 0, N = 1 only) ----
     cpu = None
@@ -362,20 +502,30 @@ def main():
         from oracle import fes_oracle_c as foc
 
         threads = host_threads()
-        n_traj, n_int = size_cpu_sample(proto, threads, target_s=12.0)
+        n_traj, n_int = size_cpu_sample(proto, threads, target_s=10.0)
         rate, secs = cpu_reference_rate(proto, n_traj, n_int, threads)
         rate1, secs1 = cpu_reference_rate(proto, max(1, n_traj // max(threads, 1) // 4), n_int, 1)  # scalar row, SURVEY 8d (ii)
         cpu = {"value": rate, "unit": UNIT, "cores": threads, "kind": "port", "seconds": secs,
+               "build": foc.timed_lib()[1] + " (compiled on this machine; the parity oracle is the strict -O2 -ffp-contract=off build)",
                "single_thread": {"value": rate1, "seconds": secs1},
                "sample": f"{n_traj} trajectories x first {n_int} intervals ({n_int * 10} RK4 steps) with d x/d x0, "
                          "reference formulation (N-term exp sum per RHS, dual-number tangents), OpenMP over trajectories"}
+        try:
+            n_h = max(threads, int(rate * 40 / max(rate1, 1.0)) // max(threads, 1) * max(threads, 1))
+            rate_h, secs_h, flags_h = cpu_hoisted_rate(proto, min(n_h * 8, 1 << 16), n_int, threads)
+            cpu["hoisted"] = {"value": rate_h, "unit": UNIT, "cores": threads, "seconds": secs_h, "build": flags_h,
+                              "what": "the kernel's own formulation (fes_core.cuh: hoisted pulse sum, reduced tangents, step "
+                                      "propagator) compiled for the host: GPU / hoisted = hardware, hoisted / port = formulation"}
+        except Exception as e:  # the row is informative; the baseline above stands without it
+            cpu["hoisted"] = {"unavailable": f"{type(e).__name__}: {e}"}
 
     if rank == 0:
         line = {
             "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
             "ms_per_step": elapsed_ms / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
             "dtype": args.dtype, "data": "synthetic", "config": workload_config(args, proto), "clocks": clocks,
-            "e2e": e2e, "gpu_launches": int(launches), "roofline": roofline, "cpu_baseline": cpu,
+            "e2e": e2e, "gpu_launches": int(launches), "roofline": roofline, "cpu_baseline": cpu, "strong": strong,
+            "configs": configs, "configs_meta": configs_meta,
             "final_force_mean": float(res.x_final[1].mean().item()),
         }
         print(json.dumps(line), flush=True)

@@ -91,6 +91,8 @@ PROTOTYPES = {
     "fes_identify_host_f32": (c_int, [POINTER(FesDesc), POINTER(FesIdentBuffers), POINTER(FesIdentOptions), c_void_p]),
     "fes_probe_fma_peak": (c_int, [c_int, c_int, c_void_p, POINTER(c_double)]),
     "fes_launch_count": (c_int64, []),
+    "fes_last_host_timing": (c_int, [POINTER(c_double)]),
+    "fes_host_pool_trim": (c_int, []),
 }
 
 _LIB = None
@@ -119,6 +121,15 @@ def lib():
         if _LIB.fes_version() != FES_ABI_VERSION:
             raise FesLibraryError("libfes_b200.so ABI version mismatch")
     return _LIB
+
+
+def is_host_emulation() -> bool:
+    """True when the loaded library is the test suite's host build of the kernel source (tests/host_emul), which the
+    tests inject explicitly; the product library does not export this symbol."""
+    try:
+        return bool(lib().fes_is_host_emulation())
+    except AttributeError:
+        return False
 
 
 def check(rc: int, what: str):

@@ -1,7 +1,9 @@
 // fes_api.cu -- the C ABI of include/fes_b200.h: argument checks, workspace carving, table build,
 // dispatch to the (kind, fatigue, direction-set) kernel instantiations, host-buffer variants, probes.
 #include <atomic>
+#include <chrono>
 #include <cstring>
+#include <mutex>
 #include <vector>
 
 #include "fes_abi_common.hpp"
@@ -130,30 +132,105 @@ int ident_impl(const FesDesc *d, const FesIdentBuffers *b, const FesIdentOptions
 }
 
 // ---- host-buffer variants: stream-ordered temporaries, H2D, kernels, D2H --------------------
+// The staging buffers come from a memory pool the LIBRARY owns (one per device, created on first use) whose release
+// threshold is unbounded: memory freed by one call stays mapped for the next one.  With the device's default pool
+// (threshold 0) every cudaStreamSynchronize handed the ~0.8 GB of a config-2 call back to the driver and the next
+// call had to map it again -- round 1 measured 0.56 s of that per call on one box (e2e = 0.75 of the device rate).
+// fes_host_pool_trim() gives the memory back.
+constexpr int MAX_DEV = 64;
+cudaMemPool_t g_pool[MAX_DEV] = {};
+std::mutex g_pool_mu;
+
+int host_pool(cudaMemPool_t *out) {
+    int dev = 0;
+    int rc = (int)cudaGetDevice(&dev);
+    if (rc) return rc;
+    if (dev < 0 || dev >= MAX_DEV) return (int)cudaErrorInvalidDevice;
+    std::lock_guard<std::mutex> lk(g_pool_mu);
+    if (g_pool[dev] == nullptr) {
+        cudaMemPoolProps props;
+        std::memset(&props, 0, sizeof(props));
+        props.allocType = cudaMemAllocationTypePinned;
+        props.handleTypes = cudaMemHandleTypeNone;
+        props.location.type = cudaMemLocationTypeDevice;
+        props.location.id = dev;
+        cudaMemPool_t pool = nullptr;
+        rc = (int)cudaMemPoolCreate(&pool, &props);
+        if (rc) return rc;
+        uint64_t keep = UINT64_MAX;
+        rc = (int)cudaMemPoolSetAttribute(pool, cudaMemPoolAttrReleaseThreshold, &keep);
+        if (rc) {
+            cudaMemPoolDestroy(pool);
+            return rc;
+        }
+        g_pool[dev] = pool;
+    }
+    *out = g_pool[dev];
+    return 0;
+}
+
+// phases of the last host-buffer call of this thread, in milliseconds (fes_last_host_timing)
+struct HostTiming {
+    double alloc = 0, h2d = 0, kernels = 0, d2h = 0, total = 0;
+};
+thread_local HostTiming t_last;
+
 struct DevPool {
     cudaStream_t s;
+    cudaMemPool_t pool = nullptr;
     std::vector<void *> ptrs;
+    cudaEvent_t ev[4] = {nullptr, nullptr, nullptr, nullptr};
+    std::chrono::steady_clock::time_point t0;
     int err = 0;
-    explicit DevPool(cudaStream_t st) : s(st) {}
+    explicit DevPool(cudaStream_t st) : s(st), t0(std::chrono::steady_clock::now()) {
+        err = host_pool(&pool);
+        for (int i = 0; i < 4 && !err; ++i) err = (int)cudaEventCreate(&ev[i]);
+    }
     void *alloc(size_t bytes) {
         if (err || bytes == 0) return nullptr;
         void *p = nullptr;
-        err = (int)cudaMallocAsync(&p, bytes, s);
+        err = (int)cudaMallocFromPoolAsync(&p, bytes, pool, s);
         if (!err) ptrs.push_back(p);
         return p;
     }
-    void *upload(const void *h, size_t bytes) {
-        if (h == nullptr) return nullptr;
-        void *p = alloc(bytes);
-        if (p && !err) err = (int)cudaMemcpyAsync(p, h, bytes, cudaMemcpyHostToDevice, s);
-        return p;
+    void upload_to(void *d, const void *h, size_t bytes) {
+        if (d && h && !err) err = (int)cudaMemcpyAsync(d, h, bytes, cudaMemcpyHostToDevice, s);
     }
     void download(void *h, const void *d, size_t bytes) {
         if (h && d && !err) err = (int)cudaMemcpyAsync(h, d, bytes, cudaMemcpyDeviceToHost, s);
     }
+    void mark(int i) {
+        if (!err) err = (int)cudaEventRecord(ev[i], s);
+    }
+    // frees (stream-ordered), waits for the stream, and records the phase times of this call
+    int finish() {
+        for (void *p : ptrs) cudaFreeAsync(p, s);
+        ptrs.clear();
+        int rc = err ? err : (int)cudaStreamSynchronize(s);
+        if (!rc) {
+            float a = 0.f, b = 0.f, c = 0.f;
+            cudaEventElapsedTime(&a, ev[0], ev[1]);
+            cudaEventElapsedTime(&b, ev[1], ev[2]);
+            cudaEventElapsedTime(&c, ev[2], ev[3]);
+            t_last.h2d = a;
+            t_last.kernels = b;
+            t_last.d2h = c;
+            t_last.total = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count();
+        }
+        return rc;
+    }
     ~DevPool() {
         for (void *p : ptrs) cudaFreeAsync(p, s);
+        for (cudaEvent_t e : ev)
+            if (e) cudaEventDestroy(e);
     }
+};
+
+// one staged array: allocation first (all of them, timed as `alloc`), then the copies
+struct Staged {
+    void *dev = nullptr;
+    const void *host = nullptr;
+    size_t bytes = 0;
 };
 
 template <typename T>
@@ -163,6 +240,7 @@ int ivp_host_impl(const FesDesc *d, const FesIvpBuffers *h, void *stream) {
     if (h == nullptr || h->params == nullptr || h->x0 == nullptr || h->x_final == nullptr || h->stim_win == nullptr) return E_BUF;
     cudaStream_t s = (cudaStream_t)stream;
     const int nx = d->fatigue ? 5 : 2, nu = num_controls(d->model_kind, d->n_trunc);
+    if (nu > 0 && h->ctrl == nullptr) return E_BUF;
     const int nd = num_dirs(d->model_kind, d->fatigue, d->dirs);
     const size_t B = (size_t)d->batch, ns = (size_t)d->n_shooting, N = (size_t)d->n_trunc, tB = (size_t)d->trace_batch;
     const size_t npts = d->trace_every == 1 ? ns * d->n_steps + 1 : ns + 1;
@@ -170,29 +248,43 @@ int ivp_host_impl(const FesDesc *d, const FesIvpBuffers *h, void *stream) {
     dd.flags &= ~FES_TABLES_READY;
     FesIvpBuffers g;
     std::memset(&g, 0, sizeof(g));
-    {
-        DevPool pool(s);
-        g.params = pool.upload(h->params, sizeof(T) * FES_NP * ((d->flags & FES_PARAMS_SHARED) ? 1 : B));
-        g.x0 = pool.upload(h->x0, sizeof(T) * nx * B);
-        g.stim_win = (const double *)pool.upload(h->stim_win, sizeof(double) * ns * N * ((d->flags & FES_WIN_SHARED) ? 1 : B));
-        if (nu) g.ctrl = pool.upload(h->ctrl, sizeof(T) * ns * nu * ((d->flags & FES_CTRL_SHARED) ? 1 : B));
-        g.x_final = pool.alloc(sizeof(T) * nx * B);
-        const bool tr = d->trace_every != 0 && tB > 0;
-        if (tr && h->trace) g.trace = pool.alloc(sizeof(T) * npts * nx * tB);
-        if (nd > 0 && h->sens_final) g.sens_final = pool.alloc(sizeof(T) * nx * nd * B);
-        if (nd > 0 && tr && h->sens_trace) g.sens_trace = pool.alloc(sizeof(T) * (ns + 1) * nx * nd * tB);
-        g.workspace_bytes = fes_workspace_bytes(&dd, sizeof(T) == 4);
-        g.workspace = pool.alloc((size_t)g.workspace_bytes);
-        if (pool.err) return pool.err;
-        rc = ivp_impl<T>(&dd, &g, stream);
-        if (rc) return rc;
-        pool.download(h->x_final, g.x_final, sizeof(T) * nx * B);
-        if (g.trace) pool.download(h->trace, g.trace, sizeof(T) * npts * nx * tB);
-        if (g.sens_final) pool.download(h->sens_final, g.sens_final, sizeof(T) * nx * nd * B);
-        if (g.sens_trace) pool.download(h->sens_trace, g.sens_trace, sizeof(T) * (ns + 1) * nx * nd * tB);
-        if (pool.err) return pool.err;
-    }
-    return (int)cudaStreamSynchronize(s);
+    DevPool pool(s);
+    const size_t b_par = sizeof(T) * FES_NP * ((d->flags & FES_PARAMS_SHARED) ? 1 : B), b_x = sizeof(T) * nx * B;
+    const size_t b_win = sizeof(double) * ns * N * ((d->flags & FES_WIN_SHARED) ? 1 : B);
+    const size_t b_ctl = nu ? sizeof(T) * ns * nu * ((d->flags & FES_CTRL_SHARED) ? 1 : B) : 0;
+    const bool tr = d->trace_every != 0 && tB > 0;
+    const size_t b_tr = (tr && h->trace) ? sizeof(T) * npts * nx * tB : 0;
+    const size_t b_sf = (nd > 0 && h->sens_final) ? sizeof(T) * nx * nd * B : 0;
+    const size_t b_st = (nd > 0 && tr && h->sens_trace) ? sizeof(T) * (ns + 1) * nx * nd * tB : 0;
+    void *params = pool.alloc(b_par), *x0 = pool.alloc(b_x), *win = pool.alloc(b_win), *ctl = pool.alloc(b_ctl);
+    g.x_final = pool.alloc(b_x);
+    g.trace = pool.alloc(b_tr);
+    g.sens_final = pool.alloc(b_sf);
+    g.sens_trace = pool.alloc(b_st);
+    g.workspace_bytes = fes_workspace_bytes(&dd, sizeof(T) == 4);
+    g.workspace = pool.alloc((size_t)g.workspace_bytes);
+    t_last = HostTiming();
+    t_last.alloc = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - pool.t0).count();
+    pool.mark(0);
+    pool.upload_to(params, h->params, b_par);
+    pool.upload_to(x0, h->x0, b_x);
+    pool.upload_to(win, h->stim_win, b_win);
+    pool.upload_to(ctl, h->ctrl, b_ctl);
+    pool.mark(1);
+    if (pool.err) return pool.err;
+    g.params = params;
+    g.x0 = x0;
+    g.stim_win = (const double *)win;
+    g.ctrl = ctl;
+    rc = ivp_impl<T>(&dd, &g, stream);
+    if (rc) return rc;
+    pool.mark(2);
+    pool.download(h->x_final, g.x_final, b_x);
+    pool.download(h->trace, g.trace, b_tr);
+    pool.download(h->sens_final, g.sens_final, b_sf);
+    pool.download(h->sens_trace, g.sens_trace, b_st);
+    pool.mark(3);
+    return pool.finish();
 }
 
 template <typename T>
@@ -202,32 +294,51 @@ int shoot_host_impl(const FesDesc *d, const FesShootBuffers *h, void *stream) {
     if (h == nullptr || h->params == nullptr || h->X == nullptr || h->stim_win == nullptr) return E_BUF;
     cudaStream_t s = (cudaStream_t)stream;
     const int nx = d->fatigue ? 5 : 2, nu = num_controls(d->model_kind, d->n_trunc);
+    if (nu > 0 && h->ctrl == nullptr) return E_BUF;
     const size_t B = (size_t)d->batch, ns = (size_t)d->n_shooting, N = (size_t)d->n_trunc;
+    int groups = d->dirs;
+    if (d->model_kind == FES_DING2003) groups &= ~FES_DIR_U;
+    const int nd = num_dirs(d->model_kind, d->fatigue, groups);
     FesDesc dd = *d;
     dd.flags &= ~FES_TABLES_READY;
     FesShootBuffers g = *h;
-    {
-        DevPool pool(s);
-        g.params = pool.upload(h->params, sizeof(T) * FES_NP * ((d->flags & FES_PARAMS_SHARED) ? 1 : B));
-        g.X = pool.upload(h->X, sizeof(T) * (ns + 1) * nx * B);
-        g.stim_win = (const double *)pool.upload(h->stim_win, sizeof(double) * ns * N * ((d->flags & FES_WIN_SHARED) ? 1 : B));
-        g.ctrl = nu ? pool.upload(h->ctrl, sizeof(T) * ns * nu * ((d->flags & FES_CTRL_SHARED) ? 1 : B)) : nullptr;
-        g.G = h->G ? pool.alloc(sizeof(T) * ns * nx * B) : nullptr;
-        g.Phi = h->Phi ? pool.alloc(sizeof(T) * ns * nx * B) : nullptr;
-        const size_t jbytes = sizeof(T) * ns * nx * (size_t)h->j_cols * B;
-        // a multi-pass caller fills J column ranges one call at a time: keep what is already there
-        g.J = (h->J && d->dirs) ? pool.upload(h->J, jbytes) : nullptr;
-        g.workspace_bytes = fes_workspace_bytes(&dd, sizeof(T) == 4);
-        g.workspace = pool.alloc((size_t)g.workspace_bytes);
-        if (pool.err) return pool.err;
-        rc = shoot_impl<T>(&dd, &g, stream);
-        if (rc) return rc;
-        if (g.G) pool.download(h->G, g.G, sizeof(T) * ns * nx * B);
-        if (g.Phi) pool.download(h->Phi, g.Phi, sizeof(T) * ns * nx * B);
-        if (g.J) pool.download(h->J, g.J, jbytes);
-        if (pool.err) return pool.err;
-    }
-    return (int)cudaStreamSynchronize(s);
+    DevPool pool(s);
+    const size_t b_par = sizeof(T) * FES_NP * ((d->flags & FES_PARAMS_SHARED) ? 1 : B), b_X = sizeof(T) * (ns + 1) * nx * B;
+    const size_t b_win = sizeof(double) * ns * N * ((d->flags & FES_WIN_SHARED) ? 1 : B);
+    const size_t b_ctl = nu ? sizeof(T) * ns * nu * ((d->flags & FES_CTRL_SHARED) ? 1 : B) : 0;
+    const size_t b_g = sizeof(T) * ns * nx * B;
+    const size_t b_J = (h->J && nd > 0) ? sizeof(T) * ns * nx * (size_t)h->j_cols * B : 0;
+    void *params = pool.alloc(b_par), *X = pool.alloc(b_X), *win = pool.alloc(b_win), *ctl = pool.alloc(b_ctl);
+    g.G = h->G ? pool.alloc(b_g) : nullptr;
+    g.Phi = h->Phi ? pool.alloc(b_g) : nullptr;
+    g.J = pool.alloc(b_J);
+    g.workspace_bytes = fes_workspace_bytes(&dd, sizeof(T) == 4);
+    g.workspace = pool.alloc((size_t)g.workspace_bytes);
+    t_last = HostTiming();
+    t_last.alloc = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - pool.t0).count();
+    pool.mark(0);
+    pool.upload_to(params, h->params, b_par);
+    pool.upload_to(X, h->X, b_X);
+    pool.upload_to(win, h->stim_win, b_win);
+    pool.upload_to(ctl, h->ctrl, b_ctl);
+    // a multi-pass caller fills J column ranges one call at a time: what the other passes wrote is kept.  A call that
+    // fills every column of J has nothing to keep and uploads nothing.  (cocofest_b200.fes.shoot stages host tensors on
+    // the device ONCE and runs all passes there; this path serves single-pass C callers.)
+    if (b_J && nd < h->j_cols) pool.upload_to(g.J, h->J, b_J);
+    pool.mark(1);
+    if (pool.err) return pool.err;
+    g.params = params;
+    g.X = X;
+    g.stim_win = (const double *)win;
+    g.ctrl = ctl;
+    rc = shoot_impl<T>(&dd, &g, stream);
+    if (rc) return rc;
+    pool.mark(2);
+    pool.download(h->G, g.G, b_g);
+    pool.download(h->Phi, g.Phi, b_g);
+    pool.download(h->J, g.J, b_J);
+    pool.mark(3);
+    return pool.finish();
 }
 
 template <typename T>
@@ -242,34 +353,51 @@ int ident_host_impl(const FesDesc *d, const FesIdentBuffers *h, const FesIdentOp
     dd.flags &= ~FES_TABLES_READY;
     FesIdentBuffers g;
     std::memset(&g, 0, sizeof(g));
-    {
-        DevPool pool(s);
-        g.params = pool.upload(h->params, sizeof(T) * FES_NP * ((d->flags & FES_PARAMS_SHARED) ? 1 : B));
-        g.x0 = pool.upload(h->x0, sizeof(T) * 2 * B);
-        g.stim_win = (const double *)pool.upload(h->stim_win, sizeof(double) * ns * N * ((d->flags & FES_WIN_SHARED) ? 1 : B));
-        if (nu) g.ctrl = pool.upload(h->ctrl, sizeof(T) * ns * nu * ((d->flags & FES_CTRL_SHARED) ? 1 : B));
-        g.target = pool.upload(h->target, sizeof(T) * (ns + 1) * ((d->flags & FES_TARGET_SHARED) ? 1 : B));
-        g.weight = pool.upload(h->weight, sizeof(T) * (ns + 1));
-        g.lower = pool.upload(h->lower, sizeof(T) * FES_NP);
-        g.upper = pool.upload(h->upper, sizeof(T) * FES_NP);
-        g.params_out = pool.alloc(sizeof(T) * FES_NP * B);
-        g.cost = pool.alloc(sizeof(T) * B);
-        g.grad = pool.alloc(sizeof(T) * np * B);
-        g.hess = pool.alloc(sizeof(T) * (np * (np + 1) / 2) * B);
-        if (h->iters) g.iters = (int32_t *)pool.alloc(sizeof(int32_t) * B);
-        g.workspace_bytes = fes_workspace_bytes(&dd, sizeof(T) == 4);
-        g.workspace = pool.alloc((size_t)g.workspace_bytes);
-        if (pool.err) return pool.err;
-        rc = ident_impl<T>(&dd, &g, o, stream);
-        if (rc) return rc;
-        pool.download(h->params_out, g.params_out, sizeof(T) * FES_NP * B);
-        pool.download(h->cost, g.cost, sizeof(T) * B);
-        pool.download(h->grad, g.grad, sizeof(T) * np * B);
-        pool.download(h->hess, g.hess, sizeof(T) * (np * (np + 1) / 2) * B);
-        if (g.iters) pool.download(h->iters, g.iters, sizeof(int32_t) * B);
-        if (pool.err) return pool.err;
-    }
-    return (int)cudaStreamSynchronize(s);
+    DevPool pool(s);
+    Staged in[8] = {
+        {nullptr, h->params, sizeof(T) * FES_NP * ((d->flags & FES_PARAMS_SHARED) ? 1 : B)},
+        {nullptr, h->x0, h->x0 ? sizeof(T) * 2 * B : 0},
+        {nullptr, h->stim_win, sizeof(double) * ns * N * ((d->flags & FES_WIN_SHARED) ? 1 : B)},
+        {nullptr, h->ctrl, nu ? sizeof(T) * ns * nu * ((d->flags & FES_CTRL_SHARED) ? 1 : B) : 0},
+        {nullptr, h->target, sizeof(T) * (ns + 1) * ((d->flags & FES_TARGET_SHARED) ? 1 : B)},
+        {nullptr, h->weight, h->weight ? sizeof(T) * (ns + 1) : 0},
+        {nullptr, h->lower, h->lower ? sizeof(T) * FES_NP : 0},
+        {nullptr, h->upper, h->upper ? sizeof(T) * FES_NP : 0},
+    };
+    for (Staged &st : in) st.dev = pool.alloc(st.bytes);
+    const size_t b_p = sizeof(T) * FES_NP * B, b_c = sizeof(T) * B, b_g = sizeof(T) * np * B;
+    const size_t b_h = sizeof(T) * (np * (np + 1) / 2) * B, b_i = h->iters ? sizeof(int32_t) * B : 0;
+    g.params_out = pool.alloc(b_p);
+    g.cost = pool.alloc(b_c);
+    g.grad = pool.alloc(b_g);
+    g.hess = pool.alloc(b_h);
+    g.iters = (int32_t *)pool.alloc(b_i);
+    g.workspace_bytes = fes_workspace_bytes(&dd, sizeof(T) == 4);
+    g.workspace = pool.alloc((size_t)g.workspace_bytes);
+    t_last = HostTiming();
+    t_last.alloc = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - pool.t0).count();
+    pool.mark(0);
+    for (Staged &st : in) pool.upload_to(st.dev, st.host, st.bytes);
+    pool.mark(1);
+    if (pool.err) return pool.err;
+    g.params = in[0].dev;
+    g.x0 = in[1].dev;
+    g.stim_win = (const double *)in[2].dev;
+    g.ctrl = in[3].dev;
+    g.target = in[4].dev;
+    g.weight = in[5].dev;
+    g.lower = in[6].dev;
+    g.upper = in[7].dev;
+    rc = ident_impl<T>(&dd, &g, o, stream);
+    if (rc) return rc;
+    pool.mark(2);
+    pool.download(h->params_out, g.params_out, b_p);
+    pool.download(h->cost, g.cost, b_c);
+    pool.download(h->grad, g.grad, b_g);
+    pool.download(h->hess, g.hess, b_h);
+    pool.download(h->iters, g.iters, b_i);
+    pool.mark(3);
+    return pool.finish();
 }
 
 // ---- FMA peak probe ------------------------------------------------------------------------------
@@ -384,5 +512,24 @@ int fes_probe_fma_peak(int is_f32, int launches, void *stream, double *tflops_ou
 }
 
 int64_t fes_launch_count(void) { return g_launches.load(); }
+
+int fes_last_host_timing(double *ms5) {
+    if (ms5 == nullptr) return E_BUF;
+    ms5[0] = t_last.alloc;
+    ms5[1] = t_last.h2d;
+    ms5[2] = t_last.kernels;
+    ms5[3] = t_last.d2h;
+    ms5[4] = t_last.total;
+    return E_OK;
+}
+
+int fes_host_pool_trim(void) {
+    int dev = 0;
+    int rc = (int)cudaGetDevice(&dev);
+    if (rc) return rc;
+    std::lock_guard<std::mutex> lk(g_pool_mu);
+    if (dev < 0 || dev >= MAX_DEV || g_pool[dev] == nullptr) return E_OK;
+    return (int)cudaMemPoolTrimTo(g_pool[dev], 0);
+}
 
 }  // extern "C"

@@ -314,12 +314,6 @@ def shoot(kind, fatigue, params, X, win, dt, n_steps=10, ctrl=None, scheme=4, wa
     cp = len(np_cols)
     cw = tiles(N) * FES_TILE if "w" in want else 0
     cols = cx + cu + cp + cw
-    G = _empty((ns, nx, B), dtype, device) if defects else None
-    Phi = _empty((ns, nx, B), dtype, device) if endpoints else None
-    J = _empty((ns, nx, cols, B), dtype, device) if cols else None
-    L = _lib.lib()
-    is32 = dtype == torch.float32
-
     # passes: (dirs, tile_offset, first column)
     passes = []
     if cx and cu:
@@ -338,15 +332,47 @@ def shoot(kind, fatigue, params, X, win, dt, n_steps=10, ctrl=None, scheme=4, wa
     if not passes:
         passes.append((0, 0, 0))
 
+    L = _lib.lib()
+    is32 = dtype == torch.float32
+    if device.type == "cpu" and len(passes) > 1 and torch.cuda.is_available() and not _lib.is_host_emulation():
+        # host tensors, several passes: stage the inputs on the device ONCE, run every pass there on a device-resident J
+        # and copy each result back once (the host entry point would move the whole J both ways at every pass)
+        dev = torch.device("cuda", torch.cuda.current_device())
+        up = lambda t: None if t is None else t.to(dev, non_blocking=True)
+        r = shoot(kind, fatigue, up(params), up(X), up(win), dt, n_steps=n_steps, ctrl=up(ctrl), scheme=scheme, want=want,
+                  t_start=t_start, tauc=tauc, r0_km=r0_km, defects=defects, endpoints=endpoints, dtype=dtype)
+
+        def down(t):
+            if t is None:
+                return None
+            h = _empty(t.shape, t.dtype, device)
+            h.copy_(t, non_blocking=True)
+            return h
+
+        out = ShootResult(down(r.G), down(r.Phi), down(r.Jx), down(r.Ju), down(r.Jp), down(r.Jw), r.p_columns)
+        torch.cuda.current_stream(dev).synchronize()
+        return out
+
+    G = _empty((ns, nx, B), dtype, device) if defects else None
+    Phi = _empty((ns, nx, B), dtype, device) if endpoints else None
+    J = _empty((ns, nx, cols, B), dtype, device) if cols else None
+
     first = True
+    ws, ws_slot = None, None
     for dirs, tile_off, col0 in passes:
         desc = _desc(kind, fatigue, scheme, N, ns, n_steps, dirs, flags, B, dt, t_start, tauc, r0_km, tile_offset=tile_off)
         buf = FesShootBuffers(_ptr(params), _ptr(X), _ptr(win), _ptr(ctrl), _ptr(G) if first else None,
                               _ptr(Phi) if first else None, _ptr(J), cols, col0, None, 0)
         if device.type == "cuda":
             with torch.cuda.device(device):
+                # the window tables depend on the table layout only (per-slot weights for Hmed2018 and for pulse-time
+                # columns, sums otherwise): consecutive passes with the same layout reuse the workspace as it is
+                slot = kind == FES_HMED2018 or bool(dirs & FES_DIR_W)
                 wbytes = L.fes_workspace_bytes(ctypes.byref(desc), int(is32))
-                ws = torch.empty(max(int(wbytes), 1), dtype=torch.uint8, device=device)
+                if ws is None or slot != ws_slot:
+                    ws, ws_slot = torch.empty(max(int(wbytes), 1), dtype=torch.uint8, device=device), slot
+                else:
+                    desc.flags |= _lib.FES_TABLES_READY
                 buf.workspace, buf.workspace_bytes = ws.data_ptr(), wbytes
                 fn = L.fes_shoot_f32 if is32 else L.fes_shoot_f64
                 _lib.check(fn(ctypes.byref(desc), ctypes.byref(buf), ctypes.c_void_p(_stream_ptr(device))), "fes_shoot")
@@ -473,6 +499,14 @@ def identify(kind, params, win, dt, target, n_steps=10, ctrl=None, identify=None
         fn = L.fes_identify_host_f32 if is32 else L.fes_identify_host_f64
         _lib.check(fn(ctypes.byref(desc), ctypes.byref(buf), ctypes.byref(opt), None), "fes_identify_host")
     return IdentResult(out_p, out_c, out_g, out_h, out_i, cols)
+
+
+def last_host_timing() -> dict:
+    """Phases (ms) of this thread's last call that went through the library's host-buffer entry points (CPU tensors):
+    staging allocation, host-to-device copies, kernels, device-to-host copies, whole call."""
+    ms = (ctypes.c_double * 5)()
+    _lib.check(_lib.lib().fes_last_host_timing(ms), "fes_last_host_timing")
+    return dict(zip(("alloc_ms", "h2d_ms", "kernels_ms", "d2h_ms", "total_ms"), (float(v) for v in ms)))
 
 
 def probe_fma_peak(is_f32=False, launches=5, device=None) -> float:

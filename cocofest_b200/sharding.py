@@ -31,24 +31,35 @@ def shard_last(t: torch.Tensor, rank: int, world: int, batch: int | None = None)
 def gather_last(t: torch.Tensor, batch: int | None = None, group=None) -> torch.Tensor:
     """All-gathers per-rank batch-last shards into the full batch-last tensor on every rank.
 
-    Shards may have unequal batch sizes (shard_bounds); they are padded to the largest for the collective."""
+    ONE collective and ONE assembling copy: the local shard `[..., n_local]` is already one contiguous block, so it is
+    gathered as it is into `[world, ..., n_max]`; the batch-last result is then written once (a single strided copy when
+    the shards are equal, one copy per rank otherwise).  Shards may have unequal batch sizes (shard_bounds); with `batch`
+    given the sizes follow from `shard_bounds` and no size exchange (and no host round trip) is needed."""
     if not (dist.is_available() and dist.is_initialized()) or dist.get_world_size(group) == 1:
         return t
-    world = dist.get_world_size(group)
+    world, rank = dist.get_world_size(group), dist.get_rank(group)
     n_local = t.shape[-1]
-    sizes = [torch.zeros(1, dtype=torch.int64, device=t.device) for _ in range(world)]
-    dist.all_gather(sizes, torch.tensor([n_local], dtype=torch.int64, device=t.device), group=group)
-    sizes = [int(s.item()) for s in sizes]
+    lead = tuple(t.shape[:-1])
+    if batch is not None:
+        sizes = [hi - lo for lo, hi in (shard_bounds(batch, r, world) for r in range(world))]
+        if sizes[rank] != n_local:
+            raise RuntimeError(f"rank {rank} holds {n_local} of {batch}, shard_bounds says {sizes[rank]}")
+    else:
+        got = [torch.zeros(1, dtype=torch.int64, device=t.device) for _ in range(world)]
+        dist.all_gather(got, torch.tensor([n_local], dtype=torch.int64, device=t.device), group=group)
+        sizes = [int(s.item()) for s in got]
     n_max = max(sizes)
-    # batch-last -> batch-first so that each rank's shard is one contiguous block of the gathered buffer
-    src = t.movedim(-1, 0).contiguous()
-    if n_local < n_max:
-        pad = torch.zeros((n_max - n_local,) + tuple(src.shape[1:]), dtype=t.dtype, device=t.device)
-        src = torch.cat([src, pad], dim=0)
-    out = torch.empty((world * n_max,) + tuple(src.shape[1:]), dtype=t.dtype, device=t.device)
-    dist.all_gather_into_tensor(out, src, group=group)
-    parts = [out[r * n_max: r * n_max + sizes[r]] for r in range(world)]
-    full = torch.cat(parts, dim=0).movedim(0, -1)
-    if batch is not None and full.shape[-1] != batch:
-        raise RuntimeError(f"gathered batch {full.shape[-1]} != expected {batch}")
+    src = t.contiguous()
+    if n_local < n_max:  # only the short shards of an uneven split pay a padded copy
+        src = torch.zeros(lead + (n_max,), dtype=t.dtype, device=t.device)
+        src[..., :n_local] = t
+    out = torch.empty((world,) + lead + (n_max,), dtype=t.dtype, device=t.device)
+    dist.all_gather_into_tensor(out.view(-1), src.view(-1), group=group)   # flat: rank r's block is out[r]
+    if min(sizes) == n_max:
+        return out.movedim(0, -2).reshape(lead + (world * n_max,))
+    full = torch.empty(lead + (sum(sizes),), dtype=t.dtype, device=t.device)
+    off = 0
+    for r in range(world):
+        full[..., off:off + sizes[r]] = out[r][..., :sizes[r]]
+        off += sizes[r]
     return full

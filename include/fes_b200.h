@@ -27,7 +27,8 @@
  *     persistent and keeps no global state; calls are re-entrant; work is enqueued on `stream`
  *     (a cudaStream_t passed as void*) and NOT synchronised.
  *   - fes_*_host_* take HOST pointers (pinned for full speed), stage through stream-ordered temporary
- *     device allocations, and return after the results are in the host buffers.
+ *     device allocations from a library-owned pool that stays mapped between calls (fes_host_pool_trim
+ *     releases it), and return after the results are in the host buffers.
  *   - device layout is structure-of-arrays with the BATCH INDEX INNERMOST (coalesced): an array written
  *     [a][b][B] below stores element (i, j, batch) at ((i*b_dim + j)*B + batch).  "shared" arrays drop
  *     the batch axis entirely.
@@ -197,6 +198,15 @@ int fes_probe_fma_peak(int is_f32, int launches, void *stream, double *tflops_ou
 
 /* Kernel launches issued by this library in the calling process since load (for bench accounting). */
 int64_t fes_launch_count(void);
+
+/* Phases of the last fes_*_host_* call of the calling thread, in milliseconds:
+ *   ms5[0] allocation of the staging buffers (host clock), ms5[1] host-to-device copies, ms5[2] kernels,
+ *   ms5[3] device-to-host copies (CUDA events on `stream`), ms5[4] the whole call (host clock). */
+int fes_last_host_timing(double *ms5);
+
+/* The fes_*_host_* calls stage through a memory pool owned by the library (one per device) that keeps its memory
+ * mapped between calls; this returns it to the driver (current device). */
+int fes_host_pool_trim(void);
 
 #ifdef __cplusplus
 }

@@ -24,14 +24,37 @@ def build(force: bool = False) -> Path:
     return so
 
 
+def _bind(cdll):
+    cdll.fes_oracle_ivp.restype = ctypes.c_int
+    cdll.fes_oracle_shoot.restype = ctypes.c_int
+    cdll.fes_oracle_max_threads.restype = ctypes.c_int
+    return cdll
+
+
 def lib():
     global _LIB
     if _LIB is None:
-        _LIB = ctypes.CDLL(str(build()))
-        _LIB.fes_oracle_ivp.restype = ctypes.c_int
-        _LIB.fes_oracle_shoot.restype = ctypes.c_int
-        _LIB.fes_oracle_max_threads.restype = ctypes.c_int
+        _LIB = _bind(ctypes.CDLL(str(build())))
     return _LIB
+
+
+TIMED_CFLAGS = ["-O3", "-march=native", "-fopenmp", "-fPIC", "-std=c11"]
+_TIMED = None
+
+
+def timed_lib():
+    """The SAME source compiled for speed (-O3 -march=native, fp contraction allowed) on the machine that runs the
+    benchmark: bench.py's timed CPU baseline.  The parity oracle stays the strict -O2 -ffp-contract=off build of
+    `lib()`.  Built into oracle/_timed/ (git-ignored); returns (cdll, flags)."""
+    global _TIMED
+    if _TIMED is None:
+        out = _HERE / "_timed"
+        out.mkdir(exist_ok=True)
+        so = out / "libfes_oracle_timed.so"
+        cc = "/usr/bin/gcc" if os.path.exists("/usr/bin/gcc") else "gcc"   # the image's CC wrapper has no libgomp.spec
+        subprocess.run([cc, *TIMED_CFLAGS, "-shared", "-o", str(so), str(_HERE / "fes_oracle.c"), "-lm"], check=True)
+        _TIMED = _bind(ctypes.CDLL(str(so)))
+    return _TIMED, " ".join(TIMED_CFLAGS)
 
 
 def _p(a):
@@ -47,8 +70,9 @@ def max_threads() -> int:
 
 
 def ivp(kind, fatigue, scheme, N, ns, S, dt, tauc, r0_km, params, x0, win, u=None, seed_x0=False, pdir=(),
-        trace_B=0, trace_every=None, sens_trace=False, n_threads=0):
-    """params [B|1, 14]; x0 [B, nx]; win [B|1, ns+1, N]; u [B|1, ns, nu] -> dict(final, trace, sens_final, sens_trace)."""
+        trace_B=0, trace_every=None, sens_trace=False, n_threads=0, cdll=None):
+    """params [B|1, 14]; x0 [B, nx]; win [B|1, ns+1, N]; u [B|1, ns, nu] -> dict(final, trace, sens_final, sens_trace).
+    cdll: another build of the same source (timed_lib), default the strict parity build."""
     nx = 5 if fatigue else 2
     x0 = _c(x0).reshape(-1, nx)
     B = x0.shape[0]
@@ -71,7 +95,7 @@ def ivp(kind, fatigue, scheme, N, ns, S, dt, tauc, r0_km, params, x0, win, u=Non
         trace_every = S
     sfin = np.empty((B, nx, nd)) if nd else None
     strace = np.empty((trace_B, ns + 1, nx, nd)) if (nd and sens_trace and trace_B) else None
-    rc = lib().fes_oracle_ivp(
+    rc = (cdll or lib()).fes_oracle_ivp(
         ctypes.c_int(kind), ctypes.c_int(int(fatigue)), ctypes.c_int(scheme), ctypes.c_int(N), ctypes.c_int(ns),
         ctypes.c_int(S), ctypes.c_double(dt), ctypes.c_double(tauc), ctypes.c_double(r0_km), ctypes.c_longlong(B),
         _p(params), ctypes.c_int(int(params.shape[0] == 1 and B != 1 or params.shape[0] == 1)),

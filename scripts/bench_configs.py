@@ -1,14 +1,18 @@
 #!/usr/bin/env python
-"""Times the hot path on the BASELINE.json configurations other than the headline one (configs 1, 3, 4, 5;
-SURVEY.md section 8d) on one B200 and prints one JSON line per configuration.
+"""The BASELINE.json configurations other than the headline one (configs 1, 3, 4, 5) plus the
+headline workload in its forward-only and fp32 forms, as timed sub-records.  bench.py imports `run_configs` and puts
+the records under "configs" of its JSON line; run directly it prints one JSON line per configuration:
 
-    python scripts/bench_configs.py [--configs 1,3,4,5] [--scale 1.0] [--steps 3] [--warmup 3] [--dtype f64]
+    python scripts/bench_configs.py [--configs 1,2fwd,3,4,4b,4c,5,5pf] [--scale 1.0] [--steps 3] [--warmup 3] [--dtype f64]
 
-Inputs are resident in HBM, timing is by CUDA events on torch's current stream (the stream the library
-launches on), a 256 MiB buffer is rewritten between timed iterations to flush L2.  `--scale` shrinks the batch
-(smoke runs); the committed numbers under profiles/ use scale 1.
+Inputs are resident in HBM, timing is by CUDA events on torch's current stream (the stream the library launches on), a
+256 MiB buffer is rewritten between timed iterations to flush L2.  Roofline fractions use the instruction counts of the
+SHIPPED SASS (cocofest_b200/csrc/sass_counts.json, written by the Makefile right after the link and refused when the
+library's sha256 differs) against the nominal pipe rate SMs x 64 (fp64) | 128 (fp32) lanes x SM clock -- a fraction can
+therefore not exceed 1.
 """
 import argparse
+import hashlib
 import json
 import statistics
 import sys
@@ -22,13 +26,46 @@ import torch  # noqa: E402
 from cocofest_b200 import _lib, fes, protocols  # noqa: E402
 
 UNIT = "trajectory-steps/s"
+KIND_NAME = {fes.FES_DING2003: "DING2003", fes.FES_DING2007: "DING2007", fes.FES_HMED2018: "HMED2018"}
 
 
-def flop_alg(nx, n_dir):
-    """4*(24 + 8*[n_dir>0] + 23*n_dir) + 13*nx*(1+n_dir) for the fatigue model; the two-state
-    models drop the three fatigue rows from the RHS (24 -> 15) as the survey's nx = 2 figure does."""
-    rhs = 24 if nx == 5 else 15
-    return 4 * (rhs + (8 if n_dir else 0) + 23 * n_dir) + 13 * nx * (1 + n_dir)
+def load_sass_counts():
+    """(counts by kernel name, reason) -- counts is None with a stated reason when the file is missing or does not
+    describe the library that is loaded."""
+    path = _lib.LIB_PATH.parent / "sass_counts.json"
+    if not path.exists():
+        return None, f"{path.name} not found next to the library (make -C cocofest_b200/csrc writes it)"
+    data = json.loads(path.read_text())
+    sha = hashlib.sha256(_lib.LIB_PATH.read_bytes()).hexdigest()
+    if data.get("lib_sha256") != sha:
+        return None, f"{path.name} describes another build (sha256 {str(data.get('lib_sha256'))[:12]}.. != loaded {sha[:12]}..)"
+    return data["kernels"], f"{path.name}, sha256 {sha[:16]}.. = the loaded {_lib.LIB_PATH.name}"
+
+
+def kernel_name(entry, dtype, kind, fatigue=None, groups=None):
+    t = "double" if dtype in ("f64", torch.float64) else "float"
+    if entry == "ident":
+        return f"fes_ident_kernel<{t}, {KIND_NAME[kind]}>"
+    bits = ((1, "X0"), (2, "U"), (4, "P"), (16, "PF"), (8, "W"))
+    g = "|".join(n for b, n in bits if groups & b) or "0"
+    return f"fes_{entry}_kernel<{t}, {KIND_NAME[kind]}, {'fatigue' if fatigue else 'no_fatigue'}, {g}>"
+
+
+def nominal_peaks(dev, sm_mhz=None):
+    """Nominal pipe rates of this GPU at `sm_mhz` (default: its maximum SM clock): thread-instructions/s of the fp64 pipe
+    (64 lanes per SM and clock = ncu's sm__inst_executed_pipe_fp64 peak) and of the fp32 FMA pipe (128 lanes)."""
+    sms = torch.cuda.get_device_properties(dev).multi_processor_count
+    if sm_mhz is None:
+        try:
+            import pynvml
+
+            pynvml.nvmlInit()
+            sm_mhz = pynvml.nvmlDeviceGetMaxClockInfo(pynvml.nvmlDeviceGetHandleByIndex(dev.index or 0), pynvml.NVML_CLOCK_SM)
+        except Exception:
+            sm_mhz = 1965
+    hz = sm_mhz * 1e6
+    return {"sms": sms, "sm_mhz": sm_mhz, "fp64_inst_s": sms * 64 * hz, "fp32_inst_s": sms * 128 * hz,
+            "fp64_tflops": sms * 64 * 2 * hz / 1e12, "fp32_tflops": sms * 128 * 2 * hz / 1e12}
 
 
 def timed(fn, steps, warmup, flush):
@@ -48,23 +85,171 @@ def timed(fn, steps, warmup, flush):
     return out, ms
 
 
-def line(name, units, ms, nx, nd, out_bytes, in_bytes, peak, dtype, extra):
+def record(name, kernel, units, ms, out_bytes, in_bytes, dtype, counts, peaks, hbm_peak_gbs, extra):
+    """One sub-record.  roofline: executed flops of the shipped SASS (2 per FMA, 1 per MUL / ADD) per trajectory-step x
+    trajectory-steps / time against the nominal pipe peak; issue_frac: the same in issue slots (every FMA / MUL / ADD holds
+    one lane of the pipe for one clock) -- the two agree up to the FMA share of the mix."""
     t = statistics.mean(ms) * 1e-3
-    fl = flop_alg(nx, nd)
-    return {
-        "config": name, "metric": "trajectory_steps_per_s", "value": units / t, "unit": UNIT, "ms_per_step": 1e3 * t,
-        "ms_all": ms, "dtype": dtype, "trajectory_steps": units, "sensitivity_columns": nd,
-        "roofline": {"bound": "fp64" if dtype == "f64" else "fp32", "flop_alg_per_trajectory_step": fl,
-                     "achieved": fl * units / t / 1e12, "peak": peak, "unit": "TFLOP/s",
-                     "frac": fl * units / t / 1e12 / peak if peak else None,
-                     "hbm_bytes": in_bytes + out_bytes, "hbm_gbs": (in_bytes + out_bytes) / t / 1e9},
-        **extra,
-    }
+    rec = {"config": name, "value": units / t, "unit": UNIT, "ms": 1e3 * t, "ms_all": [round(m, 4) for m in ms], "dtype": dtype,
+           "trajectory_steps": units, "kernel": kernel}
+    f64 = dtype == "f64"
+    k = counts.get(kernel) if counts else None
+    hbm = {"algorithmic_bytes": in_bytes + out_bytes, "achieved_gbs": (in_bytes + out_bytes) / t / 1e9, "peak_gbs": hbm_peak_gbs,
+           "frac": (in_bytes + out_bytes) / t / 1e9 / hbm_peak_gbs if hbm_peak_gbs else None}
+    if k:
+        inst = k["fp64_inst"] if f64 else k["fp32_inst"]
+        flop = k["fp64_flop"] if f64 else k["fp32_flop"]
+        peak_t = peaks["fp64_tflops"] if f64 else peaks["fp32_tflops"]
+        peak_i = peaks["fp64_inst_s"] if f64 else peaks["fp32_inst_s"]
+        ach = flop * units / t / 1e12
+        rec["roofline"] = {"bound": "fp64" if f64 else "fp32", "achieved": ach, "peak": peak_t, "unit": "TFLOP/s", "frac": ach / peak_t,
+                           "issue_frac": inst * units / t / peak_i, "inst_per_trajectory_step": inst,
+                           "flop_executed_per_trajectory_step": flop, "registers": k.get("registers"),
+                           "stack_bytes": k.get("stack_bytes")}
+        if hbm["frac"] and hbm["frac"] > rec["roofline"]["issue_frac"]:
+            rec["roofline"]["bound"] = "hbm"
+    else:
+        rec["roofline"] = None
+    rec["hbm"] = hbm
+    rec.update(extra)
+    return rec
+
+
+def run_configs(wanted, dev, dtype="f64", steps=3, warmup=3, scale=1.0, flush=None, t2=300):
+    """Runs the configurations in `wanted` (strings: "1", "2fwd", "2x0", "3", "4", "4b", "4c", "5", "5pf") on `dev`; returns
+    (records, meta)."""
+    dt_t = torch.float64 if dtype == "f64" else torch.float32
+    esz = 8 if dtype == "f64" else 4
+    if flush is None:
+        flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)
+    counts, counts_src = load_sass_counts()
+    peaks = nominal_peaks(dev)
+    hbm_peak = None
+    try:
+        hbm_peak = json.loads((ROOT / "MEASURED_PEAKS.json").read_text()).get("hbm_gbs")
+    except Exception:
+        pass
+    S = 10
+    recs = []
+    add = lambda *a: recs.append(record(*a[:7], counts, peaks, hbm_peak, a[7]))
+
+    if "1" in wanted:
+        # README IVP: DingModelFrequencyWithFatigue, stim 0..0.9 s at 10 Hz, N = 20, T = 1 -> ns = 10, all 101 points
+        B = max(1024, int((1 << 20) * scale))
+        stim = [k / 10 for k in range(10)]
+        ns = fes.prepare_n_shooting(stim, 1.0)
+        win, _ = fes.stim_windows(stim, ns, 1.0, 20)
+        win = torch.tensor(win, device=dev)
+        p = torch.tensor(fes.default_params(fes.FES_DING2003), device=dev).to(dt_t)
+        x0 = torch.zeros((5, B), dtype=dt_t, device=dev)
+        x0[2], x0[3], x0[4] = p[0], p[2], p[1]
+        fn = lambda: fes.ivp(fes.FES_DING2003, True, p, x0, win, 1.0 / ns, n_steps=S, n_shooting=ns, trace="steps", dtype=dt_t)
+        out, ms = timed(fn, steps, warmup, flush)
+        add("1: README IvpFes DingModelFrequencyWithFatigue x B, all 101 points x 5 states written",
+            kernel_name("ivp", dtype, fes.FES_DING2003, True, 0), B * ns * S, ms,
+            out.trace.numel() * esz + out.x_final.numel() * esz, x0.numel() * esz, dtype,
+            {"batch": B, "n_shooting": ns, "F_end": float(out.x_final[1, 0])})
+        del out, x0
+
+    for tag, dirs in (("2fwd", 0), ("2x0", fes.FES_DIR_X0)):
+        if tag not in wanted:
+            continue
+        # BASELINE configs[1]: forward only (as the config line states it) / with d x/d x0 (the headline, e.g. in fp32)
+        B = max(1024, int((1 << 20) * scale))
+        T = max(2, t2)
+        proto = protocols.fatigue_protocol(final_time=T)
+        p, x0 = protocols.fatigue_population(B, device=dev)
+        p, x0 = p.to(dt_t), x0.to(dt_t)
+        win = torch.tensor(proto["win"], device=dev)
+        ns = proto["ns"]
+        fn = lambda: fes.ivp(fes.FES_DING2003, True, p, x0, win, proto["dt"], n_steps=S, n_shooting=ns, trace="nodes",
+                             trace_batch=1024, dirs=dirs, dtype=dt_t)
+        out, ms = timed(fn, max(1, min(steps, 2)), max(1, min(warmup, 2)), flush)
+        ob = (out.trace.numel() + out.x_final.numel() + (out.sens_final.numel() if dirs else 0)) * esz
+        add(f"2: Ding2003+fatigue 33 Hz protocol, {T} s, 1M trajectories, " + ("with d x/d x0" if dirs else "forward only"),
+            kernel_name("ivp", dtype, fes.FES_DING2003, True, dirs), B * ns * S, ms, ob, (p.numel() + x0.numel()) * esz, dtype,
+            {"batch": B, "n_shooting": ns, "final_time_s": T, "F_end_mean": float(out.x_final[1].mean())})
+        del out, p, x0
+
+    if "3" in wanted:
+        B = max(1024, int((1 << 22) * scale))
+        proto, p, x0, ctrl = protocols.ding2007_sweep(B, device=dev)
+        p, x0, ctrl = p.to(dt_t), x0.to(dt_t), ctrl.to(dt_t)
+        win = torch.tensor(proto["win"], device=dev)
+        ns = proto["ns"]
+        fn = lambda: fes.ivp(fes.FES_DING2007, False, p, x0, win, proto["dt"], n_steps=S, ctrl=ctrl, n_shooting=ns,
+                             dirs=fes.FES_DIR_P, trace="nodes", sens_trace=True, dtype=dt_t)
+        out, ms = timed(fn, steps, warmup, flush)
+        ob = (out.trace.numel() + out.sens_trace.numel() + out.x_final.numel() + out.sens_final.numel()) * esz
+        add("3: Ding2007 pulse-width sweep, 4M parameter sets, F at 21 nodes + d F/d (a_scale, km_rest, tau1_rest, tau2, pd0, pdt)",
+            kernel_name("ivp", dtype, fes.FES_DING2007, False, fes.FES_DIR_P), B * ns * S, ms, ob, (p.numel() + x0.numel()) * esz,
+            dtype, {"batch": B, "n_shooting": ns, "columns": list(out.columns)})
+        del out, p, x0
+
+    if {"4", "4b", "4c"} & set(wanted):
+        B = max(1024, int((1 << 18) * scale))
+        proto, p, x0, ctrl = protocols.hmed2018_candidates(B, device=dev)
+        p, x0, ctrl = p.to(dt_t), x0.to(dt_t), ctrl.to(dt_t)
+        win = torch.tensor(proto["win"], device=dev)
+        ns = proto["ns"]
+        if "4" in wanted:
+            fn = lambda: fes.ivp(fes.FES_HMED2018, False, p, x0, win, proto["dt"], n_steps=S, ctrl=ctrl, n_shooting=ns,
+                                 dirs=fes.FES_DIR_P, trace="nodes", sens_trace=True, dtype=dt_t)
+            out, ms = timed(fn, steps, warmup, flush)
+            ob = (out.trace.numel() + out.sens_trace.numel() + out.x_final.numel() + out.sens_final.numel()) * esz
+            add("4: Hmed2018, 256K candidate vectors, residual inputs: F at 21 nodes + d F/d 8 parameters",
+                kernel_name("ivp", dtype, fes.FES_HMED2018, False, fes.FES_DIR_P), B * ns * S, ms, ob,
+                (p.numel() + x0.numel()) * esz, dtype, {"batch": B, "n_shooting": ns, "columns": list(out.columns)})
+        # the same candidates through the fused identification kernel: cost + gradient + Gauss-Newton matrix folded on
+        # chip (no [21 x 8] Jacobian in HBM), then 10 Levenberg-Marquardt iterations on device
+        F_true = fes.ivp(fes.FES_HMED2018, False, torch.tensor(fes.default_params(fes.FES_HMED2018), device=dev).to(dt_t),
+                         x0[:, :1].contiguous(), win, proto["dt"], n_steps=S, ctrl=ctrl, n_shooting=ns, trace="nodes", dtype=dt_t)
+        target = F_true.trace[:, 1, 0].contiguous()
+        lo = {k: v[0] for k, v in protocols.HMED_BOUNDS.items()}
+        hi = {k: v[1] for k, v in protocols.HMED_BOUNDS.items()}
+        for tag, iters in (("4b", 0), ("4c", 10)):
+            if tag not in wanted:
+                continue
+            fn = lambda: fes.identify(fes.FES_HMED2018, p, win, proto["dt"], target, n_steps=S, ctrl=ctrl, lower=lo, upper=hi,
+                                      max_iter=iters, dtype=dt_t)
+            out, ms = timed(fn, steps, warmup, flush)
+            evals = int(out.evaluations.sum().item())
+            ob = (out.params.numel() + out.cost.numel() + out.grad.numel() + out.hess.numel()) * esz
+            add(f"{tag}: Hmed2018 fes_identify, 256K candidates, max_iter={iters} (residuals + Jacobians folded into cost / gradient / "
+                "Gauss-Newton matrix on chip" + (", bounded LM loop on device)" if iters else ")"),
+                kernel_name("ident", dtype, fes.FES_HMED2018), evals * ns * S, ms, ob, (p.numel() + x0.numel()) * esz, dtype,
+                {"batch": B, "n_shooting": ns, "evaluations": evals, "median_cost": float(out.cost.median().item()),
+                 "best_cost": float(out.cost[out.best()].item())})
+        del p, x0
+
+    if {"5", "5pf"} & set(wanted):
+        B = max(1024, int((1 << 16) * scale))
+        proto, p, X, U = protocols.nmpc_scenarios(B, device=dev)
+        p, X, U = p.to(dt_t), X.to(dt_t), U.to(dt_t)
+        win = torch.tensor(proto["win"], device=dev)
+        ns = proto["ns"]
+        if "5" in wanted:
+            fn = lambda: fes.shoot(fes.FES_DING2007, True, p, X, win, proto["dt"], n_steps=S, ctrl=U, want=("x", "u"), dtype=dt_t)
+            out, ms = timed(fn, steps, warmup, flush)
+            ob = (out.G.numel() + out.Jx.numel() + out.Ju.numel()) * esz
+            add("5: NMPC cyclic horizon, 64K scenarios x 33 intervals, defects + dPhi/dx + dPhi/dpw",
+                kernel_name("shoot", dtype, fes.FES_DING2007, True, fes.FES_DIR_X0 | fes.FES_DIR_U), B * ns * S, ms, ob,
+                (X.numel() + U.numel()) * esz, dtype, {"scenarios": B, "n_shooting": ns, "interval_integrations": B * ns})
+        if "5pf" in wanted:
+            # the dense parameter columns of a fatigue model (what a fatigue-parameter identification would differentiate)
+            fn = lambda: fes.shoot(fes.FES_DING2007, True, p, X, win, proto["dt"], n_steps=S, ctrl=U, want=("p", "pf"),
+                                   defects=False, dtype=dt_t)
+            out, ms = timed(fn, steps, warmup, flush)
+            add("5pf: the same horizon, dPhi/d(6 model + 4 fatigue parameters): dense 5-component columns",
+                kernel_name("shoot", dtype, fes.FES_DING2007, True, fes.FES_DIR_P | fes.FES_DIR_PF), B * ns * S, ms,
+                out.Jp.numel() * esz, (X.numel() + U.numel()) * esz, dtype, {"scenarios": B, "n_shooting": ns})
+    meta = {"sass_counts": counts_src, "nominal_peaks": peaks}
+    return recs, meta
 
 
 def main():
     ap = argparse.ArgumentParser()
-    ap.add_argument("--configs", default="1,3,4,5")
+    ap.add_argument("--configs", default="1,3,4,4b,4c,5")
     ap.add_argument("--scale", type=float, default=1.0)
     ap.add_argument("--t2", type=int, default=300, help="protocol length of config 2 in seconds")
     ap.add_argument("--steps", type=int, default=3)
@@ -75,112 +260,12 @@ def main():
         raise SystemExit("needs a CUDA device: cocofest_b200 has no CPU fallback")
     dev = torch.device("cuda", 0)
     torch.cuda.set_device(dev)
-    dt_t = torch.float64 if args.dtype == "f64" else torch.float32
-    esz = 8 if args.dtype == "f64" else 4
-    flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)
-    peak = fes.probe_fma_peak(args.dtype == "f32", launches=5, device=dev)
-    wanted = [int(c) for c in args.configs.split(",")]
-    S = 10
-
-    if 1 in wanted:
-        # README IVP: DingModelFrequencyWithFatigue, stim 0..0.9 s at 10 Hz, N = 20, T = 1 -> ns = 10, all 101 points
-        B = max(1024, int((1 << 20) * args.scale))
-        stim = [k / 10 for k in range(10)]
-        ns = fes.prepare_n_shooting(stim, 1.0)
-        win, _ = fes.stim_windows(stim, ns, 1.0, 20)
-        win = torch.tensor(win, device=dev)
-        p = torch.tensor(fes.default_params(fes.FES_DING2003), device=dev).to(dt_t)
-        x0 = torch.zeros((5, B), dtype=dt_t, device=dev)
-        x0[2], x0[3], x0[4] = p[0], p[2], p[1]
-        fn = lambda: fes.ivp(fes.FES_DING2003, True, p, x0, win, 1.0 / ns, n_steps=S, n_shooting=ns, trace="steps", dtype=dt_t)
-        out, ms = timed(fn, args.steps, args.warmup, flush)
-        print(json.dumps(line("1: README IvpFes DingModelFrequencyWithFatigue, B replicated, all 101 points x 5 states",
-                              B * ns * S, ms, 5, 0, out.trace.numel() * esz + out.x_final.numel() * esz, x0.numel() * esz,
-                              peak, args.dtype, {"batch": B, "n_shooting": ns, "F_end": float(out.x_final[1, 0])})), flush=True)
-        del out, x0
-
-    if 2 in wanted:
-        # BASELINE configs[1] as stated: forward only (no sensitivities), F at every node for the first 1024
-        # trajectories, final state for all; --t2 shortens the protocol for sweeps
-        B = 1 << 20
-        T = max(2, args.t2)
-        proto = protocols.fatigue_protocol(final_time=T)
-        p, x0 = protocols.fatigue_population(B, device=dev)
-        p, x0 = p.to(dt_t), x0.to(dt_t)
-        win = torch.tensor(proto["win"], device=dev)
-        ns = proto["ns"]
-        fn = lambda: fes.ivp(fes.FES_DING2003, True, p, x0, win, proto["dt"], n_steps=S, n_shooting=ns, trace="nodes",
-                             trace_batch=1024, dtype=dt_t)
-        out, ms = timed(fn, args.steps, args.warmup, flush)
-        print(json.dumps(line(f"2: Ding2003+fatigue 33 Hz protocol, {T} s, forward only (no sensitivities), 1M trajectories",
-                              B * ns * S, ms, 5, 0, (out.trace.numel() + out.x_final.numel()) * esz,
-                              (p.numel() + x0.numel()) * esz, peak, args.dtype,
-                              {"batch": B, "n_shooting": ns, "final_time_s": T, "F_end_mean": float(out.x_final[1].mean())})),
-              flush=True)
-        del out, p, x0
-
-    if 3 in wanted:
-        B = max(1024, int((1 << 22) * args.scale))
-        proto, p, x0, ctrl = protocols.ding2007_sweep(B, device=dev)
-        p, x0, ctrl = p.to(dt_t), x0.to(dt_t), ctrl.to(dt_t)
-        win = torch.tensor(proto["win"], device=dev)
-        ns = proto["ns"]
-        fn = lambda: fes.ivp(fes.FES_DING2007, False, p, x0, win, proto["dt"], n_steps=S, ctrl=ctrl, n_shooting=ns,
-                             dirs=fes.FES_DIR_P, trace="nodes", sens_trace=True, dtype=dt_t)
-        out, ms = timed(fn, args.steps, args.warmup, flush)
-        ob = (out.trace.numel() + out.sens_trace.numel() + out.x_final.numel() + out.sens_final.numel()) * esz
-        print(json.dumps(line("3: Ding2007 pulse-width sweep, F at 21 nodes + d F/d (a_scale, km_rest, tau1_rest, tau2, pd0, pdt)",
-                              B * ns * S, ms, 2, 6, ob, (p.numel() + x0.numel()) * esz, peak, args.dtype,
-                              {"batch": B, "n_shooting": ns, "columns": list(out.columns)})), flush=True)
-        del out, p, x0
-
-    if 4 in wanted:
-        B = max(1024, int((1 << 18) * args.scale))
-        proto, p, x0, ctrl = protocols.hmed2018_candidates(B, device=dev)
-        p, x0, ctrl = p.to(dt_t), x0.to(dt_t), ctrl.to(dt_t)
-        win = torch.tensor(proto["win"], device=dev)
-        ns = proto["ns"]
-        fn = lambda: fes.ivp(fes.FES_HMED2018, False, p, x0, win, proto["dt"], n_steps=S, ctrl=ctrl, n_shooting=ns,
-                             dirs=fes.FES_DIR_P, trace="nodes", sens_trace=True, dtype=dt_t)
-        out, ms = timed(fn, args.steps, args.warmup, flush)
-        ob = (out.trace.numel() + out.sens_trace.numel() + out.x_final.numel() + out.sens_final.numel()) * esz
-        print(json.dumps(line("4: Hmed2018 identification candidates, F at 21 nodes + d F/d 8 parameters",
-                              B * ns * S, ms, 2, 8, ob, (p.numel() + x0.numel()) * esz, peak, args.dtype,
-                              {"batch": B, "n_shooting": ns, "columns": list(out.columns)})), flush=True)
-        # the same candidates through the fused identification kernel: cost + gradient + Gauss-Newton matrix folded in
-        # registers (no [21 x 8] Jacobian in HBM), then 10 Levenberg-Marquardt iterations on device
-        F_true = fes.ivp(fes.FES_HMED2018, False, torch.tensor(fes.default_params(fes.FES_HMED2018), device=dev).to(dt_t),
-                         x0[:, :1].contiguous(), win, proto["dt"], n_steps=S, ctrl=ctrl, n_shooting=ns, trace="nodes", dtype=dt_t)
-        target = F_true.trace[:, 1, 0].contiguous()
-        lo = {k: v[0] for k, v in protocols.HMED_BOUNDS.items()}
-        hi = {k: v[1] for k, v in protocols.HMED_BOUNDS.items()}
-        for iters in (0, 10):
-            fn = lambda: fes.identify(fes.FES_HMED2018, p, win, proto["dt"], target, n_steps=S, ctrl=ctrl, lower=lo, upper=hi,
-                                      max_iter=iters, dtype=dt_t)
-            out, ms = timed(fn, args.steps, args.warmup, flush)
-            evals = int(out.evaluations.sum().item())
-            ob = (out.params.numel() + out.cost.numel() + out.grad.numel() + out.hess.numel()) * esz
-            print(json.dumps(line(f"4{'b' if iters == 0 else 'c'}: Hmed2018 fes_identify, max_iter={iters} "
-                                  "(cost + gradient + Gauss-Newton matrix folded on device" + (", LM loop on device)" if iters else ")"),
-                                  evals * ns * S, ms, 2, 8, ob, (p.numel() + x0.numel()) * esz, peak, args.dtype,
-                                  {"batch": B, "n_shooting": ns, "evaluations": evals,
-                                   "median_cost": float(out.cost.median().item()), "best_cost": float(out.cost[out.best()].item())})),
-                  flush=True)
-        del out, p, x0
-
-    if 5 in wanted:
-        B = max(1024, int((1 << 16) * args.scale))
-        proto, p, X, U = protocols.nmpc_scenarios(B, device=dev)
-        p, X, U = p.to(dt_t), X.to(dt_t), U.to(dt_t)
-        win = torch.tensor(proto["win"], device=dev)
-        ns = proto["ns"]
-        fn = lambda: fes.shoot(fes.FES_DING2007, True, p, X, win, proto["dt"], n_steps=S, ctrl=U, want=("x", "u"), dtype=dt_t)
-        out, ms = timed(fn, args.steps, args.warmup, flush)
-        ob = (out.G.numel() + out.Jx.numel() + out.Ju.numel()) * esz
-        print(json.dumps(line("5: NMPC cyclic horizon, DingModelPulseWidthFrequencyWithFatigue, defects + dPhi/dx + dPhi/dpw",
-                              B * ns * S, ms, 5, 6, ob, (X.numel() + U.numel()) * esz, peak, args.dtype,
-                              {"scenarios": B, "n_shooting": ns, "interval_integrations": B * ns})), flush=True)
-    print(json.dumps({"gpu_launches": int(_lib.lib().fes_launch_count()), "fma_peak_tflops": peak, "dtype": args.dtype}), flush=True)
+    recs, meta = run_configs(args.configs.split(","), dev, args.dtype, args.steps, args.warmup, args.scale, t2=args.t2)
+    for r in recs:
+        print(json.dumps(r), flush=True)
+    meta["gpu_launches"] = int(_lib.lib().fes_launch_count())
+    meta["fma_probe_tflops"] = fes.probe_fma_peak(args.dtype == "f32", launches=5, device=dev)
+    print(json.dumps(meta), flush=True)
 
 
 if __name__ == "__main__":

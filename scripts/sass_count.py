@@ -1,50 +1,102 @@
 #!/usr/bin/env python
-"""Counts the fp64 pipe instructions (DFMA / DMUL / DADD) and MUFU of the RK4 path in the shipped SASS of the bench
-kernel fes_ivp_kernel<double, DING2003, fatigue, X0> and writes profiles/r01_ivp_x0_static.json (merging, so the ncu
-traffic entry written by scripts/ncu_traffic.py survives).  The RK4 path is the largest straight-line segment of the
-innermost loop (one uniform branch per step selects the scheme, fes_core.cuh rk_step)."""
+"""Static instruction counts of the RK4 path of EVERY kernel in the shipped library, tied to the library by its sha256.
+
+    python scripts/sass_count.py [--lib cocofest_b200/csrc/libfes_b200.so] [--out cocofest_b200/csrc/sass_counts.json]
+
+Run by cocofest_b200/csrc/Makefile right after the link, so the counts always describe the .so next to them; bench.py
+recomputes the library's sha256 and refuses the counts when it differs.  For every kernel: the RK4 path is the largest
+straight-line segment (between branches) of the function by floating-point instruction count -- one uniform branch
+per step selects the scheme (fes_core.cuh rk_step), so the whole RK4 step of a trajectory is ONE basic block -- and the
+record holds its instruction mix (DFMA/DMUL/DADD, FFMA/FMUL/FADD and their packed f32x2 forms, MUFU), the function's
+registers / stack frame (cuobjdump -res-usage) and its local-memory instructions (spills, LamCache).  Counts are per RK4
+step: a path that holds 4 k reciprocals (four per step, one per stage) is k steps unrolled by the compiler.
+"""
+import argparse
+import hashlib
 import json
 import re
 import subprocess
-import sys
 from collections import Counter
 from pathlib import Path
 
 ROOT = Path(__file__).resolve().parent.parent
-OBJ = ROOT / "cocofest_b200" / "csrc" / "build" / "fes_inst_k0f1.o"
-SYM = "_ZN3fes14fes_ivp_kernelIdLi0ELb1ELi1EEEvNS_7IvpArgsIT_EE"
-OUT = ROOT / "profiles" / "r01_ivp_x0_static.json"
+FP = re.compile(r"\b(DFMA|DMUL|DADD|FFMA2|FMUL2|FADD2|FFMA|FMUL|FADD|MUFU\.\w+)\b")
+KIND = {"0": "DING2003", "1": "DING2007", "2": "HMED2018"}
+GROUP_BITS = ((1, "X0"), (2, "U"), (4, "P"), (16, "PF"), (8, "W"))
 
-sass = subprocess.run(["cuobjdump", "-sass", "-fun", SYM, str(OBJ)], capture_output=True, text=True, check=True).stdout
-ins = []
-for line in sass.splitlines():
-    m = re.match(r"\s+/\*([0-9a-f]{4,})\*/\s+(.*?);", line)
-    if m:
-        ins.append((int(m.group(1), 16), m.group(2).strip()))
-fp = re.compile(r"\b(DFMA|DMUL|DADD|MUFU\.\w+)")
-inner = None
-for addr, text in ins:  # innermost loop that holds the arithmetic = smallest backward-branch body with > 200 fp64 ops
-    m = re.search(r"BRA(?:\.U)?\s+(?:!?U?P\d,\s*)?(0x[0-9a-f]+)", text)
-    if m and int(m.group(1), 16) < addr:
-        body = [x for x in ins if int(m.group(1), 16) <= x[0] <= addr]
-        if sum(1 for x in body if fp.search(x[1])) > 200 and (inner is None or len(body) < len(inner)):
-            inner = body
-segments, cur = [], []
-for addr, text in inner:
-    cur.append(text)
-    if "BRA" in text:
-        segments.append(cur)
-        cur = []
-best = max(segments, key=lambda seg: sum(1 for t in seg if fp.search(t)))
-count = Counter(fp.search(t).group(1) for t in best if fp.search(t))
-regs = re.search(SYM + r".*?Used (\d+) registers", (OBJ.parent / "fes_inst_k0f1.ptxas.log").read_text(), re.S)
-data = json.loads(OUT.read_text()) if OUT.exists() else {}
-data.update({
-    "kernel": "fes_ivp_kernel<double, DING2003, fatigue, X0>",
-    "rk4_path_instructions": len(best), "rk4_path_mix": dict(count),
-    "fp64_inst_per_rk4_step": count["DFMA"] + count["DMUL"] + count["DADD"],
-    "flop_executed_per_rk4_step": 2 * count["DFMA"] + count["DMUL"] + count["DADD"],
-    "registers": int(regs.group(1)) if regs else None,
-})
-OUT.write_text(json.dumps(data, indent=1) + "\n")
-print(json.dumps(data))
+
+def pretty(sym):
+    """_ZN3fes14fes_ivp_kernelIdLi0ELb1ELi1EEEvNS_7IvpArgsIT_EE -> fes_ivp_kernel<double, DING2003, fatigue, X0>"""
+    m = re.match(r"_ZN3fes\d+(fes_\w+_kernel)I([df])(?:Li(\d)E)?(?:Lb([01])E)?(?:Li(\d+)E)?", sym)
+    if not m:
+        return sym
+    name, t, kind, fat, groups = m.groups()
+    parts = ["double" if t == "d" else "float"]
+    if kind is not None:
+        parts.append(KIND.get(kind, kind))
+    if fat is not None:
+        parts.append("fatigue" if fat == "1" else "no_fatigue")
+    if groups is not None:
+        g = int(groups)
+        parts.append("|".join(n for b, n in GROUP_BITS if g & b) or "0")
+    return f"{name}<{', '.join(parts)}>"
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--lib", default=str(ROOT / "cocofest_b200" / "csrc" / "libfes_b200.so"))
+    ap.add_argument("--out", default=str(ROOT / "cocofest_b200" / "csrc" / "sass_counts.json"))
+    args = ap.parse_args()
+    lib = Path(args.lib)
+    sha = hashlib.sha256(lib.read_bytes()).hexdigest()
+    sass = subprocess.run(["cuobjdump", "-sass", str(lib)], capture_output=True, text=True, check=True).stdout
+    res = subprocess.run(["cuobjdump", "-res-usage", str(lib)], capture_output=True, text=True, check=True).stdout
+    usage = {}
+    for m in re.finditer(r"Function (\S+):\s*\n\s*REG:(\d+) STACK:(\d+) SHARED:(\d+) LOCAL:(\d+)", res):
+        usage[m.group(1)] = {"registers": int(m.group(2)), "stack_bytes": int(m.group(3)), "local_bytes": int(m.group(5))}
+    kernels = {}
+    for block in sass.split("Function : ")[1:]:
+        sym = block.split("\n", 1)[0].strip()
+        segs, cur, ldl, stl = [], [], 0, 0
+        for line in block.splitlines():
+            m = re.match(r"\s+/\*[0-9a-f]{4,}\*/\s+(.*?);", line)
+            if not m:
+                continue
+            text = m.group(1).strip()
+            cur.append(text)
+            ldl += bool(re.search(r"\bLDL\b", text))
+            stl += bool(re.search(r"\bSTL\b", text))
+            if re.search(r"\b(BRA|EXIT|RET|BRX|JMP)\b", text):
+                segs.append(cur)
+                cur = []
+        if cur:
+            segs.append(cur)
+        best = max(segs, key=lambda seg: sum(1 for t in seg if FP.search(t)))
+        mix = Counter(FP.search(t).group(1) for t in best if FP.search(t))
+        # every RK4 step holds exactly four reciprocals (one per stage, fes_core.cuh nominal_rhs): a path with 8 of them
+        # is two steps unrolled by the compiler (the small no-sensitivity kernels) -- counts below are PER STEP
+        rcp = sum(v for k, v in mix.items() if k.startswith("MUFU.RCP"))
+        steps = max(1, rcp // 4)
+        if steps > 1:
+            mix = Counter({k: v // steps for k, v in mix.items()})
+        fp64 = mix["DFMA"] + mix["DMUL"] + mix["DADD"]
+        fp32 = mix["FFMA"] + mix["FMUL"] + mix["FADD"]
+        fp32x2 = mix["FFMA2"] + mix["FMUL2"] + mix["FADD2"]
+        rec = {
+            "symbol": sym, "path_instructions": len(best) // steps, "steps_in_path": steps, "path_mix": dict(mix),
+            "fp64_inst": fp64, "fp64_flop": 2 * mix["DFMA"] + mix["DMUL"] + mix["DADD"],
+            "fp32_inst": fp32 + fp32x2,
+            "fp32_flop": 2 * mix["FFMA"] + mix["FMUL"] + mix["FADD"] + 2 * (2 * mix["FFMA2"] + mix["FMUL2"] + mix["FADD2"]),
+            "mufu": sum(v for k, v in mix.items() if k.startswith("MUFU")),
+            "local_loads": ldl, "local_stores": stl,
+        }
+        rec.update(usage.get(sym, {}))
+        kernels[pretty(sym)] = rec
+    out = {"lib": lib.name, "lib_sha256": sha, "how": "scripts/sass_count.py: largest straight-line segment by fp instructions "
+           "= the RK4 step of one trajectory (all tangent columns included)", "kernels": kernels}
+    Path(args.out).write_text(json.dumps(out, indent=1, sort_keys=True) + "\n")
+    print(f"{len(kernels)} kernels, lib sha256 {sha[:16]}.. -> {args.out}")
+
+
+if __name__ == "__main__":
+    main()

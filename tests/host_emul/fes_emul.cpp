@@ -51,6 +51,9 @@ template <typename T, int KIND, bool FAT, int GROUPS>
 int ivp_cpu(const IvpArgs<T> &a) {
     using D = Dirs<KIND, FAT, GROUPS>;
     constexpr int NX = D::NX, ND = D::ND;
+    // OpenMP only in the TIMED host build that bench.py compiles for the `cpu_baseline.hoisted` row (-fopenmp); the test
+    // builds are serial
+#pragma omp parallel for schedule(static)
     for (int64_t b = 0; b < a.B; ++b) {
         Traj<T> tr;
         load_traj(tr, [&](int j) { return a.params[j * a.pB + b * a.pS]; }, a.tauc, a.r0_km);
@@ -295,5 +298,7 @@ int fes_identify_host_f64(const FesDesc *d, const FesIdentBuffers *b, const FesI
 int fes_identify_host_f32(const FesDesc *d, const FesIdentBuffers *b, const FesIdentOptions *o, void *) { return ident_host<float>(d, b, o); }
 int fes_probe_fma_peak(int, int, void *, double *) { return E_DESC; }
 int64_t fes_launch_count(void) { return 0; }
+int fes_last_host_timing(double *ms5) { if (!ms5) return E_BUF; for (int i = 0; i < 5; ++i) ms5[i] = 0.0; return 0; }
+int fes_host_pool_trim(void) { return 0; }
 int fes_is_host_emulation(void) { return 1; }
 }

@@ -49,6 +49,10 @@ def _worker(rank, world, port, out_dir):
         full_x = sharding.gather_last(mine.x_final, batch=B)
         full_s = sharding.gather_last(mine.sens_final, batch=B)
         assert full_x.shape == (5, B) and full_s.shape == (5, 5, B)
+        # without `batch` the shard sizes are exchanged instead of derived; equal shards take the single-copy path
+        assert torch.equal(sharding.gather_last(mine.x_final), full_x)
+        even = sharding.gather_last(mine.sens_final[..., :18].contiguous())
+        assert even.shape == (5, 5, 36) and torch.equal(even[..., :18], full_s[..., :18]) and torch.equal(even[..., 18:], full_s[..., 19:])
         if rank == 0:
             ref = run(params, x0)
             assert torch.equal(full_x, ref.x_final) and torch.equal(full_s, ref.sens_final)
