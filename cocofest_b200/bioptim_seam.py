@@ -9,8 +9,11 @@ Reference: bioptim builds ONE ``Integrator`` per phase (``dynamics/ode_solver.py
 ``FesIntegrator`` has the same call contract and needs neither casadi nor bioptim: inputs and outputs are
 arrays, one column per scenario (the reference evaluates one column at a time).  Its Jacobian blocks are the
 ones casadi's AD of the unrolled graph yields.  ``as_casadi_function`` / ``GpuRK4`` wrap it for a machine
-that has casadi >= 3.6 and bioptim 3.2.1; they cannot be exercised in an image without them and raise
-``ImportError`` there -- nothing is evaluated on the CPU in their place.
+that has casadi >= 3.6 and bioptim 3.2.1.  Neither is installable in this image: they raise ``ImportError`` here
+(nothing is evaluated on the CPU in their place), and ``tests/test_casadi_seam.py`` executes them against strict
+stand-ins of the casadi ``Callback`` contract and of ``OdeSolver.RK4`` (``tests/standins``): declarations, call,
+``jac_<out>_<in>`` ordering, sparsities, block values, ``.map``.  A run against the real casadi
+(``Function.jacobian()`` of the stock unrolled integrator vs these blocks) stays an open item for a machine that has it.
 """
 from __future__ import annotations
 
@@ -147,7 +150,7 @@ class FesIntegrator:
         return out
 
 
-# ---- casadi / bioptim wrappers (need casadi >= 3.6 and bioptim 3.2.1; not exercised in this image) -------------
+# ---- casadi / bioptim wrappers (need casadi >= 3.6 and bioptim 3.2.1; executed against tests/standins here) -----
 def as_casadi_function(integrator: FesIntegrator, name="integrator"):
     """casadi Function with bioptim's integrator signature whose evaluation and first derivatives come from
     ``integrator``.  Only first-order sensitivities exist: run Ipopt with
@@ -159,13 +162,13 @@ def as_casadi_function(integrator: FesIntegrator, name="integrator"):
     phase time into a constraint or objective must not use this wrapper."""
     try:
         import casadi
-    except ImportError as e:  # pragma: no cover - casadi is absent from this image
+    except ImportError as e:
         raise ImportError("as_casadi_function needs casadi >= 3.6 (not installed); "
                           "use FesIntegrator / FesShooting directly") from e
     it = integrator
     sizes_in = [2, it.nx, it.nu, len(it.parameter_names), 0, it.N]
 
-    class _Jac(casadi.Callback):  # pragma: no cover
+    class _Jac(casadi.Callback):
         def __init__(self):
             casadi.Callback.__init__(self)
             self.construct(f"jac_{name}_cb", {})
@@ -199,7 +202,7 @@ def as_casadi_function(integrator: FesIntegrator, name="integrator"):
                 out.append(casadi.DM(sp) if blk is None else casadi.DM(blk[..., 0].cpu().numpy()))
             return out
 
-    class _Fun(casadi.Callback):  # pragma: no cover
+    class _Fun(casadi.Callback):
         def __init__(self):
             casadi.Callback.__init__(self)
             self._jac = None
@@ -238,7 +241,7 @@ def as_casadi_function(integrator: FesIntegrator, name="integrator"):
     return _Fun()
 
 
-def GpuRK4(n_integration_steps=10, parameter_names=(), device=None):  # pragma: no cover - needs bioptim
+def GpuRK4(n_integration_steps=10, parameter_names=(), device=None):
     """``OdeSolver.RK4`` subclass instance whose integrator evaluates on the GPU; passes cocofest's
     ``isinstance(ode_solver, (OdeSolver.RK1, RK2, RK4, COLLOCATION))`` checks (fes_ocp.py:334-338)."""
     try:

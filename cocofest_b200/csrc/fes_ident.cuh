@@ -238,6 +238,9 @@ FES_HD void ident_candidate(const IdentArgs<T> &a, int64_t b, const T *eps, T *a
         static_for<0, NPK>([&](auto id) {
             constexpr int d = decltype(id)::value;
             constexpr int j = I::canon(d);
+            // a parameter that is not identified is not projected on the box either (same rule as the initial projection):
+            // its trial value stays the starting value even when that lies outside [lower, upper]
+            if (!((a.p_mask >> d) & 1)) return;
             const T pj = cur_p(j);
             T v = pj + delta[d];
             if (a.lower != nullptr) v = v < a.lower[j] ? a.lower[j] : v;

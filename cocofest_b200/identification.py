@@ -14,9 +14,23 @@ and runs ONE Ipopt solve; here the same objective -- sum over all nodes of dt (F
 Levenberg-Marquardt iteration of ``fes_identify_*`` from ``n_starts`` starting points at once (the reference's
 initial guess first, the others drawn log-uniformly inside the box), and the best candidate is returned.
 Both reach the same minimiser when the data are informative; no Ipopt, casadi or bioptim is involved.
+
+Deliberate deviations from the reference on this path, all three pinned by ``tests/test_parity_deviations.py`` and
+listed in DESIGN.md section 5:
+  1. Hmed2018 per-node intensity matrix: slot ``j`` of node ``n`` holds the intensity of the pulse that sits in slot ``j``
+     of that node's window (right-aligned, as the window itself).  The reference's ``OcpFesId._set_u_bounds``
+     (fes_identification_ocp.py:332-343) indexes ``control_value[stim_idx[j-i][j-i]]`` / ``control_value[stim_idx[i][0]]``,
+     which pairs pulses with other pulses' intensities as soon as the intensities differ (and runs off the index lists
+     for most (i, j)); identified ``ar / bs / Is / cr`` therefore differ from the reference's on multi-intensity data.
+  2. Node assignment of pulses (``fes.stim_windows``): ``t_i <= n dt`` up to ``1e-9 dt`` instead of the reference's raw
+     float compare (ding2003.py:416), which drops the pulse at 0.1 from node 1 when dt = 0.3 / 3; the reference's own
+     golden vectors correspond to the grid-exact assignment.
+  3. ``IvpFes`` with a scalar ``pulse_intensity`` fills the control matrix with that scalar; the reference reads
+     ``self.pulse_width`` there (ivp_fes.py:339).
 """
 from __future__ import annotations
 
+import math
 import pickle
 from dataclasses import dataclass
 
@@ -199,6 +213,12 @@ class ParameterIdentification:
         for key in self.key_parameter_to_identify:
             out[key] = {name: (key_settings[key][name] if key in key_settings and name in key_settings[key] else default)
                         for name, default in self.default_values[key].items()}
+            lo, hi = float(out[key]["min_bound"]), float(out[key]["max_bound"])
+            if not (math.isfinite(lo) and math.isfinite(hi) and lo < hi):
+                raise ValueError(f"{key}: min_bound must be finite and smaller than max_bound, got [{lo}, {hi}]")
+            g = float(out[key]["initial_guess"])
+            if not (lo <= g <= hi):
+                raise ValueError(f"{key}: initial_guess {g} lies outside [{lo}, {hi}]")
         return out
 
     @staticmethod
@@ -242,7 +262,11 @@ class ParameterIdentification:
             s = self.additional_key_settings[key]
             lo, hi = float(s["min_bound"]), float(s["max_bound"])
             row = PARAM_INDEX[key]
-            draws = torch.exp(np.log(lo) + (np.log(hi) - np.log(lo)) * torch.rand(self.n_starts, generator=g, dtype=torch.float64))
+            r = torch.rand(self.n_starts, generator=g, dtype=torch.float64)
+            if lo > 0.0:   # positive box: log-uniform, the boxes span up to five decades
+                draws = torch.exp(math.log(lo) + (math.log(hi) - math.log(lo)) * r)
+            else:          # a box that reaches zero or below has no logarithm: uniform
+                draws = lo + (hi - lo) * r
             draws[0] = float(s["initial_guess"])
             P[row] = draws
         return P

@@ -144,7 +144,8 @@ class FesNmpcBatch:
 
     Reference (one scenario, Python objects rebuilt every cycle): ``FesNmpc.update_stim``
     (optimization/fes_nmpc.py:69-85: the last ``sum_stim_truncation`` pulses of the horizon, shifted back by the
-    phase time, become ``previous_stim`` of a NEW model whose window is rebuilt),
+    phase time, become ``previous_stim`` of a NEW model whose window is rebuilt; see ``update_stim`` for the one
+    deliberate deviation, the shift under a partial advance),
     ``advance_window_bounds_states`` / ``advance_window_initial_guess_states`` (:44-52, bioptim
     MultiCyclicNonlinearModelPredictiveControl: the state at frame ``n_cycles_to_advance * cycle_len`` becomes the
     fixed initial state, the remaining frames shift to the front and the tail repeats the last cycle) and
@@ -173,16 +174,45 @@ class FesNmpcBatch:
         self.shooting = self.first
         self.horizon = 0
 
-    def update_stim(self):
-        """fes_nmpc.py:69-85 -- carried pulses of the finished horizon become previous_stim of the next."""
+    def update_stim(self, pulse_intensity=None):
+        """fes_nmpc.py:69-85 -- carried pulses of the finished horizon become previous_stim of the next.
+
+        Deviation from the reference, on purpose: the reference shifts the last ``sum_stim_truncation`` pulses back by the
+        WHOLE phase time (``phase_time[0]`` = ``cycle_duration * n_cycles_simultaneous``, fes_nmpc.py:72), which is the
+        start of the next horizon only when ``n_cycles_to_advance == n_cycles_simultaneous``.  Here the shift is the time
+        the window really advances, ``cycle_duration * n_cycles_to_advance``, and every pulse that then lies before the
+        new t = 0 is a candidate (the last ``sum_stim_truncation`` of them are kept): with a partial advance the pulses
+        of the cycles that stay in the horizon are not carried twice, and closed-loop integration over the shifted
+        horizons equals one long integration (tests/test_nmpc_batch.py).  The two rules agree for a full advance.
+
+        The next model is a copy of the current one (tauc, r0_km_relationship, names and every parameter are kept), not
+        a fresh ``DingModelPulseWidthFrequencyWithFatigue`` as the reference hard-codes.  Pulse-intensity models need
+        the intensities of the carried pulses (hmed2018.py:43-47): pass ``pulse_intensity`` = one value per pulse of
+        ``stim_time`` (the solved controls); the model's own previous intensities are carried with their pulses."""
+        import copy
+
         N = self.model.sum_stim_truncation
         shift = self.cycle_duration * self.n_cycles_to_advance
+        prev_t = list(self.model.previous_stim["time"])
+        stim_t = list(self.model.stim_time)
+        is_hmed = self.model.kind == _fes.FES_HMED2018
+        if is_hmed:
+            if pulse_intensity is None or len(pulse_intensity) != len(stim_t):
+                raise ValueError("pulse-intensity models carry the intensity of every carried pulse: pass pulse_intensity "
+                                 "with one value per pulse of stim_time (hmed2018.py:43-47)")
+            prev_i = list(self.model.previous_stim.get("pulse_intensity", []))
+            prev_i = [self.model.min_pulse_intensity()] * (len(prev_t) - len(prev_i)) + prev_i
+            inten = prev_i + [float(v) for v in pulse_intensity]
         # pulses of the current horizon (and its own previous ones) that precede the next horizon's start
-        pool = [t for t in self.model.previous_stim["time"] if t > _fes.PAD_TIME] + list(self.model.stim_time)
-        carried = [t - shift for t in pool if t - shift < 0][-N:]
-        nxt = type(self.model)(previous_stim={"time": carried}, stim_time=list(self.model.stim_time), sum_stim_truncation=N)
-        for key in self.model.identifiable_parameters:
-            setattr(nxt, key, getattr(self.model, key))
+        pool = [(t, k) for k, t in enumerate(prev_t + stim_t) if t > _fes.PAD_TIME]
+        keep = [(t - shift, k) for t, k in pool if t - shift < 0][-N:]
+        carried = [t for t, _ in keep]
+        nxt = copy.copy(self.model)
+        nxt.stim_time = list(stim_t)
+        nxt.previous_stim = {"time": list(carried)}
+        if is_hmed:
+            nxt.previous_stim["pulse_intensity"] = [inten[k] for _, k in keep]
+        nxt.all_stim = list(carried) + list(stim_t)
         self.model = nxt
         self.shooting = FesShooting(nxt, self.final_time, self.n_shooting, OdeSolverLike(self.first.scheme, self.first.n_steps),
                                     device=self.device, dtype=self.first.dtype)

@@ -102,6 +102,8 @@ def levenberg_marquardt(kind, p0, win, u, target, ns, S, dt, tauc, identify=None
         pt = p.copy()
         step = 0.0
         for d, j in enumerate(cols):
+            if not active[d]:   # a parameter that is not identified is not projected on the box either
+                continue
             v = min(max(p[j] + delta[d], lo[j]), hi[j])
             step = max(step, abs(v - p[j]) / (abs(p[j]) + 1e-30))
             pt[j] = v

@@ -6,7 +6,7 @@ import pytest
 import torch
 
 import cocofest_b200 as cf
-from cocofest_b200.bioptim_seam import FesIntegrator, GpuRK4, as_casadi_function
+from cocofest_b200.bioptim_seam import FesIntegrator
 from oracle import fes_oracle as fo
 from oracle import fes_oracle_c as foc
 from tests.conftest import BACKENDS
@@ -142,17 +142,3 @@ def test_argument_checks(backend):
         it(t_span, x0, None, p, None, d)
     with pytest.raises(ValueError, match="columns"):
         it(t_span, x0, u[:, :1].repeat(3, axis=1), p, None, d)
-
-
-def test_casadi_wrappers_refuse_without_casadi():
-    try:
-        import casadi  # noqa: F401
-        pytest.skip("casadi present: the wrappers are exercised by the maintainers' own suite")
-    except ImportError:
-        pass
-    model = cf.DingModelFrequency(stim_time=[0, 0.1], sum_stim_truncation=2)
-    it = FesIntegrator(model, cf.OdeSolver.RK4(5), device="cpu")
-    with pytest.raises(ImportError, match="casadi"):
-        as_casadi_function(it)
-    with pytest.raises(ImportError, match="bioptim"):
-        GpuRK4(10)

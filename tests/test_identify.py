@@ -216,6 +216,32 @@ def test_box_is_respected(backend):
 
 
 @pytest.mark.parametrize("backend", BACKENDS, indirect=True)
+def test_fixed_parameter_outside_a_full_tensor_box_is_left_alone(backend):
+    """[14] tensor bounds cover every parameter; one that is NOT identified and starts outside its box must keep its
+    starting value (it is neither projected at the start nor clamped by a trial step) and must not count as a step."""
+    kind = fo.DING2003
+    pr = _protocol(kind)
+    truth = fo.default_params(kind)
+    target, _ = foi.node_forces(kind, truth[None], pr["win"][None], None, pr["ns"], 10, pr["dt"], pr["tauc"])
+    lo, hi = truth * 0.5, truth * 1.5
+    lo[fo.P_TAU2], hi[fo.P_TAU2] = 0.02, 0.04                # tau2 = 0.06 is fixed and lies above its box
+    lo, hi = np.minimum(lo, hi), np.maximum(lo, hi)          # alpha_a is negative
+    start = truth * np.where(np.arange(fo.NP_FULL) < 3, 1.15, 1.0)
+    ident = ["a_rest", "km_rest", "tau1_rest"]
+    res = fes.identify(kind, torch.tensor(start[:, None].copy(), device=backend), torch.tensor(pr["win"], device=backend), pr["dt"],
+                       torch.tensor(target[0], device=backend), identify=ident, lower=torch.tensor(lo), upper=torch.tensor(hi),
+                       max_iter=100)
+    got = res.params.cpu().numpy()[:, 0]
+    assert got[fo.P_TAU2] == truth[fo.P_TAU2]                # untouched
+    np.testing.assert_allclose(got[:3], truth[:3], rtol=1e-6)   # and the identified ones reach the generating values
+    ref = foi.levenberg_marquardt(kind, start, pr["win"][None], None, target, pr["ns"], 10, pr["dt"], pr["tauc"],
+                                  identify=[fes.PARAM_INDEX[k] for k in ident], lower=lo, upper=hi, max_iter=100)
+    # (near a zero-residual optimum the stopping tests are rounding-sensitive: the iterates agree, the evaluation counts need not)
+    assert ref["params"][fo.P_TAU2] == truth[fo.P_TAU2]
+    np.testing.assert_allclose(got[:3], ref["params"][:3], rtol=1e-6)
+
+
+@pytest.mark.parametrize("backend", BACKENDS, indirect=True)
 def test_argument_errors(backend):
     kind = fo.DING2003
     pr = _protocol(kind)

@@ -84,3 +84,48 @@ def test_closed_loop_equals_one_long_integration(backend):
     for c in range(3):
         got, ref = ends[c].cpu().numpy(), long.trace[33 * (c + 1)].cpu().numpy()
         assert np.max(np.abs(got - ref) / np.maximum(np.abs(ref), 1e-12)) < 1e-9
+
+
+def test_update_stim_partial_advance_shift_and_kept_attributes():
+    """n_cycles_simultaneous = 3 > n_cycles_to_advance = 1: the reference (fes_nmpc.py:72) shifts the last N pulses by the
+    whole phase time (3 s), the product by the time the window really advances (1 s) -- pinned here, with the customised
+    model attributes the next horizon's model must keep."""
+    # a train that is NOT the same in every cycle (the third cycle stimulates at 11 Hz): on a periodic train the two rules
+    # pick different pulses with identical times
+    stim = [k / 33 for k in range(66)] + [2 + k / 11 for k in range(11)]
+    model = cf.DingModelPulseWidthFrequencyWithFatigue(stim_time=stim, sum_stim_truncation=10)
+    model.tauc, model.r0_km_relationship, model.a_scale = 0.013, 1.1, 4000.0
+    model._muscle_name = "biceps"
+    nm = FesNmpcBatch(model, 1.0, n_cycles_simultaneous=3, n_cycles_to_advance=1, device="cpu")
+    carried = nm.update_stim()
+    np.testing.assert_allclose(carried, [t - 1.0 for t in stim if t < 1.0][-10:], atol=1e-12)     # the last N pulses BEFORE t = 1 s
+    reference_rule = [t - 3.0 for t in stim[-10:]]                                                # fes_nmpc.py:71-72
+    assert not np.allclose(carried, reference_rule)
+    assert np.allclose(np.array(carried) - np.round(np.array(carried) * 33) / 33, 0, atol=1e-12)  # still on the 33 Hz grid
+    nxt = nm.model
+    assert (nxt.tauc, nxt.r0_km_relationship, nxt.a_scale, nxt.muscle_name) == (0.013, 1.1, 4000.0, "biceps")
+    assert type(nxt) is type(model) and nxt is not model and model.previous_stim["time"] != nxt.previous_stim["time"]
+    # a full advance is where the two rules agree
+    again = cf.DingModelPulseWidthFrequencyWithFatigue(stim_time=stim, sum_stim_truncation=10)
+    full = FesNmpcBatch(again, 1.0, n_cycles_simultaneous=3, n_cycles_to_advance=3, device="cpu")
+    np.testing.assert_allclose(full.update_stim(), reference_rule, atol=1e-12)
+
+
+def test_update_stim_carries_pulse_intensities_for_hmed():
+    stim = [k / 20 for k in range(20)]
+    model = cf.DingModelPulseIntensityFrequencyWithFatigue(stim_time=stim, sum_stim_truncation=6,
+                                                           previous_stim={"time": [-0.1, -0.05], "pulse_intensity": [40.0, 45.0]})
+    nm = FesNmpcBatch(model, 1.0, device="cpu")
+    with pytest.raises(ValueError, match="pulse_intensity"):
+        nm.update_stim()
+    inten = [50.0 + k for k in range(20)]
+    carried = nm.update_stim(pulse_intensity=inten)
+    np.testing.assert_allclose(carried, [t - 1.0 for t in stim[-6:]], atol=1e-12)
+    assert nm.model.previous_stim["pulse_intensity"] == inten[-6:]
+    # a horizon shorter than the window: the model's own previous pulses are carried with their intensities
+    short = cf.DingModelPulseIntensityFrequencyWithFatigue(stim_time=[0.0, 0.5], sum_stim_truncation=4,
+                                                           previous_stim={"time": [-0.3, -0.2], "pulse_intensity": [40.0, 45.0]})
+    nm2 = FesNmpcBatch(short, 1.0, device="cpu")
+    nm2.update_stim(pulse_intensity=[60.0, 70.0])
+    np.testing.assert_allclose(nm2.model.previous_stim["time"], [-1.3, -1.2, -1.0, -0.5], atol=1e-12)
+    assert nm2.model.previous_stim["pulse_intensity"] == [40.0, 45.0, 60.0, 70.0]
