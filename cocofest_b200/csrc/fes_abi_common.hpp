@@ -42,7 +42,10 @@ inline int check_desc(const FesDesc *d, bool ivp) {
     if (d == nullptr || d->abi_version != FES_ABI_VERSION) return E_DESC;
     if (d->model_kind < 0 || d->model_kind > 2 || (d->fatigue != 0 && d->fatigue != 1)) return E_MODEL;
     if (d->scheme != 1 && d->scheme != 2 && d->scheme != 4) return E_MODEL;
-    if (d->n_trunc < 1 || d->n_trunc > 64 || d->n_shooting < 1 || d->n_steps < 1 || d->n_steps > 256) return E_SIZE;
+    // per-slot window tables (Hmed2018 intensities, pulse-time columns) are staged per thread: 64 slots at most; the other
+    // models only see the two sums of the window, whatever its length (the truncation sweep goes to 300 pulses)
+    const int max_trunc = slot_tables(d->model_kind, d->dirs) ? 64 : 1024;
+    if (d->n_trunc < 1 || d->n_trunc > max_trunc || d->n_shooting < 1 || d->n_steps < 1 || d->n_steps > 256) return E_SIZE;
     if (d->batch < 1 || !(d->dt > 0.0) || !(d->tauc > 0.0)) return E_SIZE;
     if (num_dirs(d->model_kind, d->fatigue, d->dirs) < 0) return E_DIRS;
     if (ivp && (d->dirs & (FES_DIR_U | FES_DIR_W))) return E_DIRS;
@@ -203,7 +206,7 @@ inline const char *strerror_abi(int code) {
         case E_OK: return "ok";
         case E_DESC: return "null descriptor or abi_version mismatch";
         case E_MODEL: return "invalid model_kind / fatigue / scheme";
-        case E_SIZE: return "invalid size (n_trunc 1..64, n_steps 1..256, n_shooting, batch, dt, tauc, tile_offset, J columns)";
+        case E_SIZE: return "invalid size (n_trunc 1..64 [1..1024 for ding2003 / ding2007 without pulse-time columns], n_steps 1..256, n_shooting, batch, dt, tauc, tile_offset, J columns)";
         case E_DIRS: return "unsupported sensitivity direction set for this model / entry point";
         case E_BUF: return "a required buffer is NULL";
         case E_WORKSPACE: return "workspace is NULL or smaller than fes_workspace_bytes";

@@ -87,7 +87,7 @@ typedef struct FesDesc {
     int32_t model_kind;  /* FES_DING2003 | FES_DING2007 | FES_HMED2018 */
     int32_t fatigue;     /* 0 | 1 */
     int32_t scheme;      /* 1 = RK1, 2 = RK2 (midpoint), 4 = RK4  (bioptim integrator.py:324-365) */
-    int32_t n_trunc;     /* N = sum_stim_truncation, window length, 1..64 */
+    int32_t n_trunc;     /* N = sum_stim_truncation, window length, 1..64 (1..1024 for FES_DING2003 / FES_DING2007 without FES_DIR_W) */
     int32_t n_shooting;  /* ns = number of intervals */
     int32_t n_steps;     /* S = RK steps per interval (n_integration_steps), 1..256 */
     int32_t dirs;        /* sensitivity groups, 0 = none */

@@ -39,7 +39,7 @@
 enum { P_A_REST, P_KM_REST, P_TAU1_REST, P_TAU2, P_ALPHA_A, P_ALPHA_TAU1, P_ALPHA_KM, P_TAU_FAT,
        P_PD0, P_PDT, P_AR, P_BS, P_IS, P_CR, NP_FULL };
 enum { DING2003 = 0, DING2007 = 1, HMED2018 = 2 };
-#define MAXN 64   /* window length limit of the oracle */
+#define MAXN 320  /* window length limit of the oracle (the truncation sweep reaches 100) */
 #define MAXD 40   /* max tangent directions of the oracle */
 
 /* ------------------------------------------------------------------ plain double path ---------- */

@@ -59,7 +59,7 @@ int main(int argc, char **argv) {
         int refused = 0;
         bad = d; bad.abi_version = 99;  refused += fes_ivp_host_f64(&bad, &b, NULL) < 0;
         bad = d; bad.scheme = 3;        refused += fes_ivp_host_f64(&bad, &b, NULL) < 0;
-        bad = d; bad.n_trunc = 65;      refused += fes_ivp_host_f64(&bad, &b, NULL) < 0;
+        bad = d; bad.n_trunc = 1025;     refused += fes_ivp_host_f64(&bad, &b, NULL) < 0;
         bad = d; bad.n_steps = 257;     refused += fes_ivp_host_f64(&bad, &b, NULL) < 0;
         bad = d; bad.dirs = FES_DIR_U;  refused += fes_ivp_host_f64(&bad, &b, NULL) < 0;
         bad = d; bad.model_kind = 7;    refused += fes_ivp_host_f64(&bad, &b, NULL) < 0;
