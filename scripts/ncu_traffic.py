@@ -1,7 +1,8 @@
 #!/usr/bin/env python
-"""Merges the figures of one `ncu --set full` capture of the bench kernel into profiles/r01_ivp_x0_static.json
-(`ncu_full_capture`), which bench.py reads for `roofline.traffic`.
-Usage: ncu_traffic.py report.ncu-rep summary.tsv [batch] [final_time_s]"""
+"""Writes the DRAM traffic of one `ncu --set full` capture of the bench kernel to profiles/r02_ivp_x0_traffic.json together
+with the sha256 of the library it was captured from (cocofest_b200/csrc/sass_counts.json); bench.py reports it as
+`roofline.traffic` only while the loaded library has that sha256.
+Usage: ncu_traffic.py report.ncu-rep summary.tsv [batch] [final_time_s] [dtype]"""
 import csv
 import io
 import json
@@ -10,10 +11,11 @@ import sys
 from pathlib import Path
 
 ROOT = Path(__file__).resolve().parent.parent
-OUT = ROOT / "profiles" / "r01_ivp_x0_static.json"
+OUT = ROOT / "profiles" / "r02_ivp_x0_traffic.json"
 rep, summary = sys.argv[1], sys.argv[2]
 batch = int(sys.argv[3]) if len(sys.argv) > 3 else 1 << 20
 final_time = int(sys.argv[4]) if len(sys.argv) > 4 else 300
+dtype = sys.argv[5] if len(sys.argv) > 5 else "f64"
 raw = subprocess.run(["ncu", "-i", rep, "--page", "raw", "--csv"], capture_output=True, text=True, check=True).stdout
 rows = list(csv.reader(io.StringIO(raw[raw.index('"ID"'):])))
 hdr, units, vals = rows[0], rows[1], rows[2]
@@ -31,9 +33,9 @@ def get(name, scale=None):
 
 
 rd, wr = get("dram__bytes_read.sum", "bytes"), get("dram__bytes_write.sum", "bytes")
-d = json.loads(OUT.read_text()) if OUT.exists() else {}
-d["ncu_full_capture"] = {
-    "report": f"{rep} (summary: {summary})", "batch": batch, "final_time_s": final_time,
+sha = json.loads((ROOT / "cocofest_b200" / "csrc" / "sass_counts.json").read_text())["lib_sha256"]
+d = {
+    "report": f"{rep} (summary: {summary})", "batch": batch, "final_time_s": final_time, "dtype": dtype, "lib_sha256": sha,
     "dram_bytes_read": int(rd), "dram_bytes_write": int(wr), "dram_bytes": int(rd + wr),
     "gpu_time_duration_s": get("gpu__time_duration.sum", "seconds"),
     "fp64_pipe_active_pct": get("sm__pipe_fp64_cycles_active.avg.pct_of_peak_sustained_active"),
@@ -41,4 +43,4 @@ d["ncu_full_capture"] = {
     "waves_per_sm": round(get("launch__waves_per_multiprocessor"), 2),
 }
 OUT.write_text(json.dumps(d, indent=1) + "\n")
-print(json.dumps(d["ncu_full_capture"]))
+print(json.dumps(d))
