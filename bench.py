@@ -272,6 +272,11 @@ def main():
     if args.impl == "reference":
         run_reference(args)
         return
+    # stdout carries exactly ONE line, the JSON record: whatever libraries print there (NCCL's version banner under
+    # torchrun) goes to stderr instead -- file descriptor 1 is pointed at stderr and the record is written to the real one
+    sys.stdout.flush()
+    real_stdout = os.fdopen(os.dup(1), "w")
+    os.dup2(2, 1)
 
     import torch
     import torch.distributed as dist
@@ -528,7 +533,8 @@ def main():
             "configs": configs, "configs_meta": configs_meta,
             "final_force_mean": float(res.x_final[1].mean().item()),
         }
-        print(json.dumps(line), flush=True)
+        real_stdout.write(json.dumps(line) + "\n")
+        real_stdout.flush()
     if world > 1:
         dist.barrier()
         dist.destroy_process_group()

@@ -109,15 +109,22 @@ constexpr bool dirs_forced_cn() {
     return n >= 3;
 }
 // Fatigue models: the rows A', Tau1', Km' are linear with the SAME decay 1/tau_fat and are all driven by F
-// alone, so for every direction that does not force those rows (initial states, controls, pulse times) the
-// tangent (vA, vTau1, vKm) stays in a 1-dimensional affine family:
+// alone, so the tangent (vA, vTau1, vKm) of EVERY direction stays in an affine family around one scalar W:
 //     vA = alpha_a W + mA,  vTau1 = alpha_tau1 W + mT1,  vKm = alpha_km W + mKm,
-//     W' = vF - W/tau_fat  (W = 0 at the seed),   m' = -m/tau_fat  (m = the seeded component).
-// Runge-Kutta maps commute with constant linear embeddings, so pushing (vCn, vF, W) and ONE shared decaying
-// scalar through the stages gives the tangent of the discrete map exactly (not an approximation of it);
-// such a "reduced" column carries 2 or 3 numbers instead of 5.  The Cn0 column's own Cn component is the
-// second shared scalar (vCn' = -vCn/tauc), which leaves that column with (vF, W) as well.
-constexpr bool dir_reduced(bool fat, int c) { return fat && c <= D_WT; }
+//     W' = vF - W/tau_fat  (W = 0 at the seed),   m' = -m/tau_fat + f_d(t)  (m = the seeded component at the seed),
+// where f_d is what the direction adds to the fatigue rows THEMSELVES -- it does not depend on the tangent:
+//     initial states, controls, pulse times, tau2, pd0, pdt, ar..cr   f = 0:  m = the seed times the decaying mode mu
+//     a_rest | tau1_rest | km_rest      f = 1/tau_fat on its own row:  m = 1 - mu            (the same mode again)
+//     alpha_a | alpha_tau1 | alpha_km   f = F(t) on its own row:  m = M, M' = F - M/tau_fat  (ONE scalar for the three)
+//     tau_fat                           f = (x - x_rest)/tau_fat^2 on the three rows: three scalars of its own
+// Runge-Kutta maps commute with constant linear embeddings, so pushing (vCn, vF, W) and the few shared decaying
+// scalars through the stages gives the tangent of the discrete map exactly (not an approximation of it);
+// such a "reduced" column carries 2 or 3 numbers instead of 5 (tau_fat: 5).  The Cn0 column's own Cn component is
+// another shared scalar (vCn' = -vCn/tauc), which leaves that column with (vF, W) as well.
+constexpr bool dir_reduced(bool fat, int c) { return fat && c >= 0; }
+constexpr bool dir_rest(int c) { return c == D_A_REST || c == D_TAU1_REST || c == D_KM_REST; }
+constexpr bool dir_alpha(int c) { return c == D_ALPHA_A || c == D_ALPHA_TAU1 || c == D_ALPHA_KM; }
+constexpr bool dir_own_m(int c) { return c == D_TAU_FAT; }  // mA, mT1, mKm kept in V[d][0], V[d][3], V[d][4]
 template <class D>
 constexpr bool dirs_all_reduced() {
     for (int d = 0; d < D::ND; ++d)
@@ -136,12 +143,18 @@ constexpr bool dirs_have(int c) {
         if (D::code(d) == c) return true;
     return false;
 }
-// components stored in V[d][...] for a column of code c: [first, last)
-constexpr int dir_first(bool fat, int c) {
-    if (dir_reduced(fat, c)) return (dir_has_cn(c) && c != D_CN0) ? 0 : 1;
-    return dir_has_cn(c) ? 0 : 1;
+// is component j of V[d][...] advanced stage by stage for a column of code c?  (sh: the forced Cn components of this
+// direction set ride on the shared modes and are advanced once per step instead)
+constexpr bool dir_stores(bool fat, int c, int j, bool sh) {
+    if (j == 0) {
+        if (fat && dir_own_m(c)) return true;
+        if (fat && c == D_CN0) return false;  // the shared scalar nu
+        return dir_has_cn(c) && !(sh && dir_forced_cn(c));
+    }
+    if (j == 1) return true;
+    if (!fat) return false;
+    return j == 2 || dir_own_m(c);
 }
-constexpr int dir_last(bool fat, int c) { return dir_reduced(fat, c) ? 3 : (fat ? 5 : 2); }
 
 template <int I, int N, class F>
 FES_HD void static_for(F &&f) {
@@ -464,9 +477,11 @@ FES_HD void column_rhs(const Traj<T> &tr, const Stage<T> &st, T eps, T sE, T dg,
 }
 
 // ---- one RK stage of one REDUCED tangent column (fatigue models, see dir_reduced) ------------
-// v = (vCn, vF, W); mu / nu = the shared decaying scalars (fatigue mode, Cn mode) at this stage point.
+// v = (vCn | mA, vF, W, mT1, mKm); mu / nu = the shared decaying scalars (fatigue mode, Cn mode) and Ms = the shared
+// alpha-column scalar M and rest-column scalar R, all at this stage point.
 template <typename T, int KIND, int CODE, bool S0, bool SH>
-FES_HD void column_rhs_red(const Traj<T> &tr, const Stage<T> &st, T eps, T sE, T dg, T pc_dl, T pc_psi, T mu, T nu, const T *v, T *k) {
+FES_HD void column_rhs_red(const Traj<T> &tr, const Stage<T> &st, T eps, T sE, T dg, T pc_dl, T pc_psi, T mu, T nu, T Ms,
+                           T Rs, const T *v, T *k) {
     T kf = xfma(st.cW, v[2], st.cF * v[1]);
     if constexpr (CODE == D_CN0) {
         kf = xfma(st.cCn, nu, kf);
@@ -480,13 +495,22 @@ FES_HD void column_rhs_red(const Traj<T> &tr, const Stage<T> &st, T eps, T sE, T
     if constexpr (CODE == D_A0) kf = xfma(st.cA, mu, kf);
     if constexpr (CODE == D_TAU10) kf = xfma(st.cT1, mu, kf);
     if constexpr (CODE == D_KM0) kf = xfma(st.cKm, mu, kf);
+    if constexpr (dir_rest(CODE)) kf = xfma(CODE == D_A_REST ? st.cA : (CODE == D_TAU1_REST ? st.cT1 : st.cKm), Rs, kf);
+    if constexpr (dir_alpha(CODE)) kf = xfma(CODE == D_ALPHA_A ? st.cA : (CODE == D_ALPHA_TAU1 ? st.cT1 : st.cKm), Ms, kf);
+    if constexpr (dir_own_m(CODE)) {
+        kf = xfma(st.cA, v[0], xfma(st.cT1, v[3], xfma(st.cKm, v[4], kf)));
+        k[0] = xfma(-tr.kappa, v[0], st.dA);
+        k[3] = xfma(-tr.kappa, v[3], st.dT1);
+        k[4] = xfma(-tr.kappa, v[4], st.dKm);
+    }
+    if constexpr (CODE == D_TAU2) kf += st.cT2;
     if constexpr (dir_has_dg(CODE)) kf = xfma(st.cG, dg, kf);
     k[1] = kf;
     k[2] = xfma(-tr.kappa, v[2], v[1]);
 }
 
 // ---- tangent state of one trajectory ----------------------------------------------------------
-// V[d] holds the stored components of column d (dir_first .. dir_last); mu, nu are the two shared decaying
+// V[d] holds the stored components of column d (dir_stores); mu, nu are the two shared decaying
 // scalars of the reduced columns.  They are kept in double in the f32 build too: a float cannot represent
 // 1 - h/tau_fat (h/tau_fat ~ 2e-5) to better than 0.3 % of the decay rate, and the fp64 pipe is idle there.
 template <typename T, int KIND, bool FAT, int GROUPS>
@@ -494,8 +518,23 @@ struct Tangent {
     using D = Dirs<KIND, FAT, GROUPS>;
     T V[D::ND > 0 ? D::ND : 1][D::NX];
     double mu, nu;
+    T M;  // shared by the alpha_a / alpha_tau1 / alpha_km columns: M' = F - M/tau_fat, 0 at the seed
+    T R;  // shared by the a_rest / tau1_rest / km_rest columns:     R' = (1 - R)/tau_fat, 0 at the seed (= 1 - mu, kept on
+          // its own so that it is exact near the seed, where 1 - mu cancels)
 
-    FES_HD void init() {
+    // f32 build, fatigue models: A, Tau1, Km are ACCUMULATED in double.  Their per-step increments (alpha_X F h ~ 1e-4 of the
+    // state) sit a few bits above a float's resolution of the state, so a float accumulator loses ~3e-4 of every increment:
+    // measured 9e-5 relative drift of A after 20 s of the fatigue protocol, growing linearly.  The increments themselves are
+    // formed in float; only the three running sums (3 DADD per step on the otherwise idle fp64 pipe) are double.
+    double xd[3];
+
+    // x = the state the integration starts from (seeds the double accumulators of the f32 build)
+    FES_HD void init(const T *x) {
+        if constexpr (FAT && sizeof(T) == 4) {
+            xd[0] = (double)x[2];
+            xd[1] = (double)x[3];
+            xd[2] = (double)x[4];
+        }
         static_for<0, D::ND>([&](auto ic) {
             constexpr int d = decltype(ic)::value;
             constexpr int C = D::code(d);
@@ -507,6 +546,8 @@ struct Tangent {
         });
         mu = 1.0;
         nu = 1.0;
+        M = T(0);
+        R = T(0);
     }
     // component j of the actual tangent column d (what the caller sees)
     template <int d>
@@ -515,12 +556,16 @@ struct Tangent {
         if constexpr (!dir_reduced(FAT, C)) {
             return V[d][j];
         } else {
-            if (j == 0) return C == D_CN0 ? (T)nu : (dir_has_cn(C) ? V[d][0] : T(0));
+            if (j == 0) return C == D_CN0 ? (T)nu : ((dir_has_cn(C) && !dir_own_m(C)) ? V[d][0] : T(0));
             if (j == 1) return V[d][1];
-            const T m = (T)mu;
-            if (j == 2) return xfma(tr.alpha_a, V[d][2], C == D_A0 ? m : T(0));
-            if (j == 3) return xfma(tr.alpha_tau1, V[d][2], C == D_TAU10 ? m : T(0));
-            return xfma(tr.alpha_km, V[d][2], C == D_KM0 ? m : T(0));
+            // the component the direction seeds or forces on the fatigue row j (see dir_reduced)
+            T m = T(0);
+            if constexpr (C == D_A0 || C == D_TAU10 || C == D_KM0) m = (j == 2 + (C - D_A0)) ? (T)mu : T(0);
+            if constexpr (dir_rest(C)) m = (j == (C == D_A_REST ? 2 : (C == D_TAU1_REST ? 3 : 4))) ? R : T(0);
+            if constexpr (dir_alpha(C)) m = (j == 2 + (C - D_ALPHA_A)) ? M : T(0);
+            if constexpr (dir_own_m(C)) m = j == 2 ? V[d][0] : V[d][j];
+            const T al = j == 2 ? tr.alpha_a : (j == 3 ? tr.alpha_tau1 : tr.alpha_km);
+            return xfma(al, V[d][2], m);
         }
     }
 };
@@ -561,7 +606,9 @@ FES_HD void rk_step_scheme(const Traj<T> &tr, const Interval<T, Dirs<KIND, FAT, 
     constexpr int ND = D::ND;
     constexpr int NS = TB::NS;
     constexpr bool NEED = ND > 0;
-    constexpr bool MODES = FAT && (D::n_x0 > 0);
+    constexpr bool ANY_REST = dirs_have<D>(D_A_REST) || dirs_have<D>(D_TAU1_REST) || dirs_have<D>(D_KM_REST);
+    constexpr bool ANY_ALPHA = dirs_have<D>(D_ALPHA_A) || dirs_have<D>(D_ALPHA_TAU1) || dirs_have<D>(D_ALPHA_KM);
+    constexpr bool MODES = FAT && (D::n_x0 > 0);  // the shared decaying scalars mu, nu are advanced
     T xs[NX], xn[NX];
 #pragma unroll
     for (int j = 0; j < NX; ++j) xs[j] = xn[j] = x[j];
@@ -576,24 +623,42 @@ FES_HD void rk_step_scheme(const Traj<T> &tr, const Interval<T, Dirs<KIND, FAT, 
     double mus = tg.mu, mun = tg.mu, nus = tg.nu, nun = tg.nu;
     // Cn' = (E eps - Cn)/tauc is a linear row with tabulated forcing: Cn(stage s) = Cn dl_s + E psi_s (stage table)
     // Nominal fatigue rows, reduced within the step exactly like the tangent ones: with the offsets d = x - rest at
-    // the step start,  A(stage) = A_rest + dA m_s + alpha_a Wn,  Wn' = F - Wn/tau_fat (Wn = 0 at the step start),
+    // the step start,  A(stage) = A_rest + dA m_s + alpha_a Wn = A - dA (1 - m_s) + alpha_a Wn,  Wn' = F - Wn/tau_fat (Wn = 0 at the step start),
     // m_s = the scheme's stage values of m' = -m/tau_fat from m = 1 (loop-invariant, hoisted by the compiler).
     constexpr int NXN = FAT ? 2 : NX;  // nominal components advanced by the generic update below
     T fm[NS + 1];                      // fm[s] = m at stage s, fm[NS] = m after the step
     T dA = T(0), dT1 = T(0), dKm = T(0), wn_s = T(0), wn_n = T(0);
+    T wnv[NS + 1];  // Wn at the stage points (wnv[0] = 0) and after the step: the forcing of the alpha / tau_fat columns
+    wnv[0] = T(0);
+    T em[NS + 1];  // em[s] = 1 - fm[s], formed WITHOUT the cancellation (a float holds z = h/tau_fat ~ 2e-5 exactly enough,
+                   // but not 1 - z): the modes that start at 0 (R, M, the tau_fat scalars) are advanced with em
     if constexpr (FAT) {
         const T z = tr.kappa * h;
         fm[0] = T(1);
-        T acc = T(1);
+        em[0] = T(0);
+        T acc = T(1), eacc = T(0);
         static_for<0, NS>([&](auto is) {
             constexpr int s = decltype(is)::value;
-            if constexpr (TB::beta(s) != 0.0) acc = xfma(-z * T(TB::beta(s)), fm[s], acc);
-            if constexpr (s + 1 < NS) fm[s + 1] = xfma(-z * T(TB::alpha(s + 1)), fm[s], T(1));
+            if constexpr (TB::beta(s) != 0.0) {
+                acc = xfma(-z * T(TB::beta(s)), fm[s], acc);
+                eacc = xfma(z * T(TB::beta(s)), fm[s], eacc);
+            }
+            if constexpr (s + 1 < NS) {
+                fm[s + 1] = xfma(-z * T(TB::alpha(s + 1)), fm[s], T(1));
+                em[s + 1] = (z * T(TB::alpha(s + 1))) * fm[s];
+            }
         });
         fm[NS] = acc;
-        dA = x[2] - tr.a_rest;
-        dT1 = x[3] - tr.tau1_rest;
-        dKm = x[4] - tr.km_rest;
+        em[NS] = eacc;
+        if constexpr (sizeof(T) == 4) {
+            dA = (T)(tg.xd[0] - (double)tr.a_rest);
+            dT1 = (T)(tg.xd[1] - (double)tr.tau1_rest);
+            dKm = (T)(tg.xd[2] - (double)tr.km_rest);
+        } else {
+            dA = x[2] - tr.a_rest;
+            dT1 = x[3] - tr.tau1_rest;
+            dKm = x[4] - tr.km_rest;
+        }
     }
 
     // dl[s] = the scheme's stage values of v' = -v/tauc from 1 (loop-invariant); ps[s-1] = psi at stage s and ps[3] =
@@ -612,6 +677,20 @@ FES_HD void rk_step_scheme(const Traj<T> &tr, const Interval<T, Dirs<KIND, FAT, 
         dl[NS] = acc;
     }
 
+    auto finish_fatigue = [&]() {  // the fatigue states after the step: x - em d + alpha_X Wn
+        if constexpr (FAT && sizeof(T) == 4) {
+            tg.xd[0] += (double)xfma(tr.alpha_a, wn_n, -(em[NS] * dA));
+            tg.xd[1] += (double)xfma(tr.alpha_tau1, wn_n, -(em[NS] * dT1));
+            tg.xd[2] += (double)xfma(tr.alpha_km, wn_n, -(em[NS] * dKm));
+            x[2] = (T)tg.xd[0];
+            x[3] = (T)tg.xd[1];
+            x[4] = (T)tg.xd[2];
+        } else if constexpr (FAT) {
+            x[2] = xfma(tr.alpha_a, wn_n, xfma(dA, fm[NS], tr.a_rest));
+            x[3] = xfma(tr.alpha_tau1, wn_n, xfma(dT1, fm[NS], tr.tau1_rest));
+            x[4] = xfma(tr.alpha_km, wn_n, xfma(dKm, fm[NS], tr.km_rest));
+        }
+    };
     // the two halves of a stage: the nominal RHS (fills the Jacobian record st) and the tangent columns (consume it)
     auto nominal_stage = [&](auto is, Stage<T> &st) {
         constexpr int s = decltype(is)::value;
@@ -626,9 +705,18 @@ FES_HD void rk_step_scheme(const Traj<T> &tr, const Interval<T, Dirs<KIND, FAT, 
                 if constexpr (TB::beta(s) != 0.0) wn_n = s == 0 ? hb * kw : xfma(hb, kw, wn_n);
                 if constexpr (!LAST) {
                     wn_s = ha * kw;
-                    xs[2] = xfma(tr.alpha_a, wn_s, xfma(dA, fm[s + 1], tr.a_rest));
-                    xs[3] = xfma(tr.alpha_tau1, wn_s, xfma(dT1, fm[s + 1], tr.tau1_rest));
-                    xs[4] = xfma(tr.alpha_km, wn_s, xfma(dKm, fm[s + 1], tr.km_rest));
+                    wnv[s + 1] = wn_s;
+                    // f32 build: rest + d fm_s = x - em_s d, the decay applied as a small correction of the state itself (em = 1 - fm
+                    // is exact in a float, fm is not: its rounding would bias the recovery rate by up to 0.1 %)
+                    if constexpr (sizeof(T) == 4) {
+                        xs[2] = xfma(tr.alpha_a, wn_s, xfma(-em[s + 1], dA, x[2]));
+                        xs[3] = xfma(tr.alpha_tau1, wn_s, xfma(-em[s + 1], dT1, x[3]));
+                        xs[4] = xfma(tr.alpha_km, wn_s, xfma(-em[s + 1], dKm, x[4]));
+                    } else {  // fp64 holds fm to 1e-16: the direct form keeps em out of the register budget
+                        xs[2] = xfma(tr.alpha_a, wn_s, xfma(dA, fm[s + 1], tr.a_rest));
+                        xs[3] = xfma(tr.alpha_tau1, wn_s, xfma(dT1, fm[s + 1], tr.tau1_rest));
+                        xs[4] = xfma(tr.alpha_km, wn_s, xfma(dKm, fm[s + 1], tr.km_rest));
+                    }
                 }
             }
             if constexpr (!LAST) xs[0] = xfma(x[0], dl[s + 1], iv.E * ps[s]);
@@ -645,7 +733,10 @@ FES_HD void rk_step_scheme(const Traj<T> &tr, const Interval<T, Dirs<KIND, FAT, 
         const T hb = h * T(TB::beta(s));
         const T ha = h * T(LAST ? 0.0 : TB::alpha(s + 1));
         const T eps = e[TB::eps_at(s)];
-        T mu_s = T(0), nu_s = T(0);
+        T mu_s = T(0), nu_s = T(0), M_s = T(0), R_s = T(0);
+        // M(s) = M fm_s + Wn(s),  R(s) = R fm_s + (1 - fm_s), written with em = 1 - fm
+        if constexpr (FAT && ANY_ALPHA) M_s = s == 0 ? tg.M : xfma(-em[s], tg.M, tg.M) + wnv[s];
+        if constexpr (FAT && ANY_REST) R_s = s == 0 ? tg.R : xfma(em[s], T(1) - tg.R, tg.R);
         if constexpr (MODES && sizeof(T) == 8) {
             // the decaying scalars are the step-start values times the loop-invariant stage factors fm / dl
             mu_s = s == 0 ? (T)tg.mu : (T)tg.mu * fm[s];
@@ -672,17 +763,18 @@ FES_HD void rk_step_scheme(const Traj<T> &tr, const Interval<T, Dirs<KIND, FAT, 
             constexpr int C = D::code(d);
             // stored components of this column: Cn only for the directions that reach it; (vF, W) when reduced;
             // a forced Cn component (vs[d][0] = its value at the step start) is advanced once, after the stages
-            constexpr int J0 = (CNF && dir_forced_cn(C)) ? 1 : dir_first(FAT, C), J1 = dir_last(FAT, C);
             T k[NX];
             if constexpr (dir_reduced(FAT, C))
-                column_rhs_red<T, KIND, C, s == 0, CNF>(tr, st, eps, iv.sE[d], iv.dg[d], pc_dl, pc_psi, mu_s, nu_s, vs[d], k);
+                column_rhs_red<T, KIND, C, s == 0, CNF>(tr, st, eps, iv.sE[d], iv.dg[d], pc_dl, pc_psi, mu_s, nu_s, M_s, R_s, vs[d], k);
             else
                 column_rhs<T, KIND, FAT, C, s == 0, CNF>(tr, st, eps, iv.sE[d], iv.dg[d], pc_dl, pc_psi, vs[d], k);
-#pragma unroll
-            for (int j = J0; j < J1; ++j) {
-                if constexpr (TB::beta(s) != 0.0) vn[d][j] = xfma(hb, k[j], vn[d][j]);
-                if constexpr (!LAST) vs[d][j] = xfma(ha, k[j], tg.V[d][j]);
-            }
+            static_for<0, NX>([&](auto ij) {
+                constexpr int j = decltype(ij)::value;
+                if constexpr (dir_stores(FAT, C, j, CNF)) {
+                    if constexpr (TB::beta(s) != 0.0) vn[d][j] = xfma(hb, k[j], vn[d][j]);
+                    if constexpr (!LAST) vs[d][j] = xfma(ha, k[j], tg.V[d][j]);
+                }
+            });
         });
     };
 #ifndef FES_NO_PROPAGATOR  // measured against the stage-by-stage columns: config 3 +20 %, config 4 +15 %, fes_identify +13 %
@@ -738,8 +830,7 @@ FES_HD void rk_step_scheme(const Traj<T> &tr, const Interval<T, Dirs<KIND, FAT, 
         return;
     }
 #ifndef FES_NO_PROP2  // measured against the stage-by-stage reduced columns (profiles/r01_tune_prop2_ag.txt): headline +15 %
-    constexpr bool PROP2 = FAT && ND > 0 && SCHEME == 4 && dirs_all_reduced<D>() &&
-                           (CNF || !dirs_any_forced_cn<D>());
+    constexpr bool PROP2 = FAT && ND > 0 && SCHEME == 4;
 #else
     constexpr bool PROP2 = false;
 #endif
@@ -763,7 +854,11 @@ FES_HD void rk_step_scheme(const Traj<T> &tr, const Interval<T, Dirs<KIND, FAT, 
         const T t11_0 = xfma(p1_0, sq[0].cF, r1_0), t11_1 = xfma(p1_1, sq[0].cF, r1_1);
         const T t12_0 = xfma(p1_0, sq[0].cW, -(kp * r1_0)), t12_1 = xfma(p1_1, sq[0].cW, -(kp * r1_1));
         const T Phi00 = T(1) + ((t11_0 + t21_0) + (t31_0 + t41_0)), Phi10 = (t11_1 + t21_1) + (t31_1 + t41_1);
-        const T Phi01 = (t12_0 + t22_0) + (t32_0 + t42_0), Phi11 = T(1) + ((t12_1 + t22_1) + (t32_1 + t42_1));
+        // f32 build: W decays by ~2e-5 per step, a factor a float cannot hold (1 - 2e-5 rounds to 0.1 % of the rate): W is
+        // advanced as W + (dPhi11 W + ...) with dPhi11 = Phi11 - 1 formed without the cancellation
+        constexpr bool WINC = sizeof(T) == 4;
+        const T dPhi11 = (t12_1 + t22_1) + (t32_1 + t42_1);
+        const T Phi01 = (t12_0 + t22_0) + (t32_0 + t42_0), Phi11 = WINC ? dPhi11 : T(1) + dPhi11;
         const T pF[NS] = {p1_0, p2_0, p3_0, h6}, pW[NS] = {p1_1, p2_1, p3_1, T(0)};
         // S(X) = sum_s p_s X_s for the forcing profiles the columns of this set use
         auto wsum = [&](auto coef, T &sF, T &sW) {
@@ -775,24 +870,76 @@ FES_HD void rk_step_scheme(const Traj<T> &tr, const Interval<T, Dirs<KIND, FAT, 
         constexpr bool ANY_CN = dirs_have<D>(D_CN0) || dirs_any_forced_cn<D>();
         T sCdF = T(0), sCdW = T(0), sCpF = T(0), sCpW = T(0), sAF = T(0), sAW = T(0), sT1F = T(0), sT1W = T(0);
         T sKmF = T(0), sKmW = T(0), sGF = T(0), sGW = T(0);
+        constexpr bool ANY_DG = dirs_have<D>(D_PW) || dirs_have<D>(D_PD0) || dirs_have<D>(D_PDT);
         if constexpr (ANY_CN)
             wsum([&](auto q) { constexpr int s = decltype(q)::value; return s == 0 ? sq[0].cCn : sq[s].cCn * dl[s]; }, sCdF, sCdW);
         if constexpr (dirs_any_forced_cn<D>()) {
             sCpF = xfma(pF[3], sq[3].cCn * ps[2], xfma(pF[2], sq[2].cCn * ps[1], pF[1] * (sq[1].cCn * ps[0])));
             sCpW = xfma(pW[2], sq[2].cCn * ps[1], pW[1] * (sq[1].cCn * ps[0]));
         }
-        if constexpr (dirs_have<D>(D_A0) || dirs_have<D>(D_TAU10) || dirs_have<D>(D_KM0)) {
-            // the three fatigue-seed columns share the weights p_s m_s (m_s = the stage values of the decaying mode)
-            const T qF[NS] = {pF[0], pF[1] * fm[1], pF[2] * fm[2], pF[3] * fm[3]}, qW[NS] = {pW[0], pW[1] * fm[1], pW[2] * fm[2], T(0)};
-            auto msum = [&](auto coef, T &sF, T &sW) {
-                sF = xfma(qF[3], coef(3), xfma(qF[2], coef(2), xfma(qF[1], coef(1), qF[0] * coef(0))));
-                sW = xfma(qW[2], coef(2), xfma(qW[1], coef(1), qW[0] * coef(0)));
+        // Forcing of the fatigue rows (dir_reduced): every such column adds  sum_s p_s c_X(s) m(s)  with c_X the Jacobian entry
+        // of its row (cA | cT1 | cKm) and m(s) = m0 fm_s + (what its own forcing adds within the step):
+        //     seeds A0 / Tau10 / Km0        m(s) = mu fm_s
+        //     a_rest / tau1_rest / km_rest  m(s) = R fm_s + em_s                    (em = 1 - fm)
+        //     alpha_a / alpha_tau1 / _km    m(s) = M fm_s + Wn(s)
+        // so the sums S_fm(c_X) (weights p_s fm_s), S_em(c_X) (weights p_s em_s) and S_wn(c_X) (weights p_s Wn(s)) are formed
+        // once per row and shared by the columns that use them.
+        constexpr bool ROW_A = dirs_have<D>(D_A0) || dirs_have<D>(D_A_REST) || dirs_have<D>(D_ALPHA_A);
+        constexpr bool ROW_T1 = dirs_have<D>(D_TAU10) || dirs_have<D>(D_TAU1_REST) || dirs_have<D>(D_ALPHA_TAU1);
+        constexpr bool ROW_KM = dirs_have<D>(D_KM0) || dirs_have<D>(D_KM_REST) || dirs_have<D>(D_ALPHA_KM);
+        constexpr bool OWN_M = dirs_have<D>(D_TAU_FAT);
+        const T qF[NS] = {pF[0], pF[1] * fm[1], pF[2] * fm[2], pF[3] * fm[3]}, qW[NS] = {pW[0], pW[1] * fm[1], pW[2] * fm[2], T(0)};
+        auto msum = [&](auto coef, T &sF, T &sW) {
+            sF = xfma(qF[3], coef(3), xfma(qF[2], coef(2), xfma(qF[1], coef(1), qF[0] * coef(0))));
+            sW = xfma(qW[2], coef(2), xfma(qW[1], coef(1), qW[0] * coef(0)));
+        };
+        if constexpr (ROW_A) msum([&](int s) { return sq[s].cA; }, sAF, sAW);
+        if constexpr (ROW_T1) msum([&](int s) { return sq[s].cT1; }, sT1F, sT1W);
+        if constexpr (ROW_KM) msum([&](int s) { return sq[s].cKm; }, sKmF, sKmW);
+        T eAF = T(0), eAW = T(0), eT1F = T(0), eT1W = T(0), eKmF = T(0), eKmW = T(0);   // S_em
+        if constexpr (ANY_REST) {
+            const T wF[NS] = {T(0), pF[1] * em[1], pF[2] * em[2], pF[3] * em[3]}, wW[NS] = {T(0), pW[1] * em[1], pW[2] * em[2], T(0)};
+            auto esum = [&](auto coef, T &sF, T &sW) {
+                sF = xfma(wF[3], coef(3), xfma(wF[2], coef(2), wF[1] * coef(1)));
+                sW = xfma(wW[2], coef(2), wW[1] * coef(1));
             };
-            if constexpr (dirs_have<D>(D_A0)) msum([&](int s) { return sq[s].cA; }, sAF, sAW);
-            if constexpr (dirs_have<D>(D_TAU10)) msum([&](int s) { return sq[s].cT1; }, sT1F, sT1W);
-            if constexpr (dirs_have<D>(D_KM0)) msum([&](int s) { return sq[s].cKm; }, sKmF, sKmW);
+            if constexpr (dirs_have<D>(D_A_REST)) esum([&](int s) { return sq[s].cA; }, eAF, eAW);
+            if constexpr (dirs_have<D>(D_TAU1_REST)) esum([&](int s) { return sq[s].cT1; }, eT1F, eT1W);
+            if constexpr (dirs_have<D>(D_KM_REST)) esum([&](int s) { return sq[s].cKm; }, eKmF, eKmW);
         }
-        if constexpr (dirs_have<D>(D_PW))
+        T nAF = T(0), nAW = T(0), nT1F = T(0), nT1W = T(0), nKmF = T(0), nKmW = T(0);   // S_wn
+        if constexpr (ANY_ALPHA) {
+            const T wF[NS] = {T(0), pF[1] * wnv[1], pF[2] * wnv[2], pF[3] * wnv[3]}, wW[NS] = {T(0), pW[1] * wnv[1], pW[2] * wnv[2], T(0)};
+            auto nsum = [&](auto coef, T &sF, T &sW) {
+                sF = xfma(wF[3], coef(3), xfma(wF[2], coef(2), wF[1] * coef(1)));
+                sW = xfma(wW[2], coef(2), wW[1] * coef(1));
+            };
+            if constexpr (dirs_have<D>(D_ALPHA_A)) nsum([&](int s) { return sq[s].cA; }, nAF, nAW);
+            if constexpr (dirs_have<D>(D_ALPHA_TAU1)) nsum([&](int s) { return sq[s].cT1; }, nT1F, nT1W);
+            if constexpr (dirs_have<D>(D_ALPHA_KM)) nsum([&](int s) { return sq[s].cKm; }, nKmF, nKmW);
+        }
+        T sT2F = T(0), sT2W = T(0);
+        if constexpr (dirs_have<D>(D_TAU2)) wsum([&](auto q) { return sq[decltype(q)::value].cT2; }, sT2F, sT2W);
+        // d / d tau_fat: the three rows are forced by (x - x_rest)/tau_fat^2 = kappa^2 (d_X fm(t) + alpha_X Wn(t)), hence
+        //     m_X(s) = m_X fm_s + kappa^2 (d_X sigma_s + alpha_X omega_s),
+        // sigma / omega = the scheme's stage values of y' = -y/tau_fat + fm(t) | + Wn(t) from 0 (sigma is loop-invariant).
+        T sg[NS + 1] = {}, om[NS + 1] = {};
+        if constexpr (OWN_M) {
+            const T ks1 = xfma(-kp, h2, fm[1]);                 // sigma_1 = h/2 (k_0 = fm_0 = 1)
+            sg[1] = h2;
+            sg[2] = h2 * ks1;
+            const T ks2 = xfma(-kp, sg[2], fm[2]);
+            sg[3] = h * ks2;
+            const T ks3 = xfma(-kp, sg[3], fm[3]);
+            sg[4] = h6 * ((T(1) + ks3) + T(2) * (ks1 + ks2));
+            const T ko1 = wnv[1];                               // omega_1 = 0 (k_0 = Wn(0) = 0)
+            om[2] = h2 * ko1;
+            const T ko2 = xfma(-kp, om[2], wnv[2]);
+            om[3] = h * ko2;
+            const T ko3 = xfma(-kp, om[3], wnv[3]);
+            om[4] = h6 * (ko3 + T(2) * (ko1 + ko2));
+        }
+        if constexpr (ANY_DG)
             wsum([&](auto q) { return sq[decltype(q)::value].cG; }, sGF, sGW);
         const T mu0 = (T)tg.mu, nu0 = (T)tg.nu;
         static_for<0, ND>([&](auto ic) {
@@ -826,14 +973,52 @@ FES_HD void rk_step_scheme(const Traj<T> &tr, const Interval<T, Dirs<KIND, FAT, 
                 aF = xfma(sGF, iv.dg[d], aF);
                 aW = xfma(sGW, iv.dg[d], aW);
             }
+            if constexpr (dir_rest(C)) {
+                const T R0 = tg.R;
+                const T fF = C == D_A_REST ? sAF : (C == D_TAU1_REST ? sT1F : sKmF), fW = C == D_A_REST ? sAW : (C == D_TAU1_REST ? sT1W : sKmW);
+                const T gF = C == D_A_REST ? eAF : (C == D_TAU1_REST ? eT1F : eKmF), gW = C == D_A_REST ? eAW : (C == D_TAU1_REST ? eT1W : eKmW);
+                aF = xfma(fF, R0, aF + gF);
+                aW = xfma(fW, R0, aW + gW);
+            }
+            if constexpr (dir_alpha(C)) {
+                const T M0 = tg.M;
+                const T fF = C == D_ALPHA_A ? sAF : (C == D_ALPHA_TAU1 ? sT1F : sKmF), fW = C == D_ALPHA_A ? sAW : (C == D_ALPHA_TAU1 ? sT1W : sKmW);
+                const T gF = C == D_ALPHA_A ? nAF : (C == D_ALPHA_TAU1 ? nT1F : nKmF), gW = C == D_ALPHA_A ? nAW : (C == D_ALPHA_TAU1 ? nT1W : nKmW);
+                aF = xfma(fF, M0, aF + gF);
+                aW = xfma(fW, M0, aW + gW);
+            }
+            if constexpr (C == D_TAU2) {
+                aF += sT2F;
+                aW += sT2W;
+            }
+            if constexpr (dir_own_m(C)) {
+                const T mA = tg.V[d][0], mT1 = tg.V[d][3], mKm = tg.V[d][4], k2 = tr.kappa2;
+                T gF = T(0), gW = T(0);
+                static_for<0, NS>([&](auto is) {
+                    constexpr int q = decltype(is)::value;
+                    const T Z = xfma(sq[q].cA, mA, xfma(sq[q].cT1, mT1, sq[q].cKm * mKm));
+                    T G = q == 0 ? Z : Z * fm[q];
+                    if constexpr (q > 0) {
+                        const T Y = xfma(sq[q].cA, dA, xfma(sq[q].cT1, dT1, sq[q].cKm * dKm));
+                        G = xfma(k2, xfma(Y, sg[q], sq[q].cW * om[q]), G);
+                    }
+                    gF = xfma(pF[q], G, gF);
+                    if constexpr (q < NS - 1) gW = xfma(pW[q], G, gW);
+                });
+                aF += gF;
+                aW += gW;
+                tg.V[d][0] = xfma(k2, xfma(dA, sg[NS], tr.alpha_a * om[NS]), xfma(-em[NS], mA, mA));
+                tg.V[d][3] = xfma(k2, xfma(dT1, sg[NS], tr.alpha_tau1 * om[NS]), xfma(-em[NS], mT1, mT1));
+                tg.V[d][4] = xfma(k2, xfma(dKm, sg[NS], tr.alpha_km * om[NS]), xfma(-em[NS], mKm, mKm));
+            }
             tg.V[d][1] = aF;
-            tg.V[d][2] = aW;
+            tg.V[d][2] = WINC ? vW + aW : aW;
         });
+        if constexpr (ANY_ALPHA) tg.M = xfma(-em[NS], tg.M, tg.M) + wn_n;
+        if constexpr (ANY_REST) tg.R = xfma(em[NS], T(1) - tg.R, tg.R);
         x[0] = xfma(x[0], dl[NS], iv.E * ps[3]);
         x[1] = xn[1];
-        x[2] = xfma(tr.alpha_a, wn_n, xfma(dA, fm[NS], tr.a_rest));
-        x[3] = xfma(tr.alpha_tau1, wn_n, xfma(dT1, fm[NS], tr.tau1_rest));
-        x[4] = xfma(tr.alpha_km, wn_n, xfma(dKm, fm[NS], tr.km_rest));
+        finish_fatigue();
         if constexpr (MODES && sizeof(T) == 8) {
             tg.mu *= (double)fm[NS];
             tg.nu *= (double)dl[NS];
@@ -868,17 +1053,19 @@ FES_HD void rk_step_scheme(const Traj<T> &tr, const Interval<T, Dirs<KIND, FAT, 
 #pragma unroll
     for (int j = 1; j < NXN; ++j) x[j] = xn[j];
     if constexpr (FAT) {
-        x[2] = xfma(tr.alpha_a, wn_n, xfma(dA, fm[NS], tr.a_rest));
-        x[3] = xfma(tr.alpha_tau1, wn_n, xfma(dT1, fm[NS], tr.tau1_rest));
-        x[4] = xfma(tr.alpha_km, wn_n, xfma(dKm, fm[NS], tr.km_rest));
+        finish_fatigue();
     }
     static_for<0, ND>([&](auto ic) {
         constexpr int d = decltype(ic)::value;
         constexpr int C = D::code(d);
         if constexpr (CNF && dir_forced_cn(C)) tg.V[d][0] = xfma(tg.V[d][0], dl[NS], iv.sE[d] * ps[3]);
-#pragma unroll
-        for (int j = (CNF && dir_forced_cn(C)) ? 1 : dir_first(FAT, C); j < dir_last(FAT, C); ++j) tg.V[d][j] = vn[d][j];
+        static_for<0, NX>([&](auto ij) {
+            constexpr int j = decltype(ij)::value;
+            if constexpr (dir_stores(FAT, C, j, CNF)) tg.V[d][j] = vn[d][j];
+        });
     });
+    if constexpr (FAT && ANY_ALPHA) tg.M = xfma(-em[NS], tg.M, tg.M) + wn_n;
+    if constexpr (FAT && ANY_REST) tg.R = xfma(em[NS], T(1) - tg.R, tg.R);
     if constexpr (MODES && sizeof(T) == 8) {
         tg.mu *= (double)fm[NS];
         tg.nu *= (double)dl[NS];

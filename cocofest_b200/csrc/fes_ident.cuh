@@ -63,7 +63,7 @@ FES_HD void ident_eval(const IdentArgs<T> &a, int64_t b, const T *pc, int pstrid
         x[1] = a.x0[a.B + b];
     }
     Tangent<T, KIND, false, G_P> tg;
-    tg.init();
+    tg.init(x);
     LamCache<T> *lcp = nullptr;
     [[maybe_unused]] LamCache<T> lc;
     // measured (profiles/r01_tune_ident_lamcache_x.txt): +2.5 % for the plain evaluation, -2.4 % inside the LM loop,

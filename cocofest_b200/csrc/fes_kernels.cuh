@@ -15,6 +15,7 @@
 
 #if defined(__CUDACC__)
 #include <cuda_runtime.h>
+#include <cuda_pipeline.h>
 #endif
 
 #include "fes_core.cuh"
@@ -77,6 +78,7 @@ struct ShootArgs {
     int64_t B;
     int N, ns, S, scheme, tile_off;
     T h, tauc, r0_km;
+    int stage_tc;                      // set by the launcher: table row + controls are staged in shared memory too
 };
 
 #if defined(__CUDACC__)
@@ -131,7 +133,7 @@ __global__ void FES_LAUNCH_BOUNDS fes_ivp_kernel(const IvpArgs<T> a) {
 #pragma unroll
     for (int j = 0; j < NX; ++j) x[j] = a.x0[j * a.B + bb];
     Tangent<T, KIND, FAT, GROUPS> tg;
-    tg.init();
+    tg.init(x);
     LamCache<T> *lcp = nullptr;
     [[maybe_unused]] LamCache<T> lc;
     if constexpr (KIND == HMED2018) {
@@ -214,6 +216,13 @@ __global__ void FES_LAUNCH_BOUNDS fes_ivp_kernel(const IvpArgs<T> a) {
 }
 
 // ---------------------------------------------------------------------------------------------
+// Every thread integrates ONE interval of S steps, so the latency of its input loads is paid once per ~3000 issued
+// instructions instead of once per trajectory: left to the compiler (under the register cap the loads sink next to their
+// first use) four dependent round trips to HBM were exposed per thread -- long_scoreboard 1.33 cycles per issue, fp64 pipe
+// 70 % active (profiles/r01_ncu_shoot_cfg5_ai_summary.tsv).  Here the thread's inputs (node state, next node state, and the
+// table row + controls when they fit) are copied global -> shared with cp.async (LDGSTS, no registers) as the first thing
+// the thread does, all in flight at once and overlapped with the stage-table load and the parameter set-up; the
+// integration then reads them from its own shared-memory column [value][thread] (conflict-free).
 template <typename T, int KIND, bool FAT, int GROUPS>
 __global__ void FES_LAUNCH_BOUNDS fes_shoot_kernel(const ShootArgs<T> a) {
     using D = Dirs<KIND, FAT, GROUPS>;
@@ -221,27 +230,50 @@ __global__ void FES_LAUNCH_BOUNDS fes_shoot_kernel(const ShootArgs<T> a) {
     constexpr int ND = D::ND;
     extern __shared__ __align__(16) unsigned char smem_raw[];
     T *s_eps = reinterpret_cast<T *>(smem_raw);
+    T *s_in = s_eps + ((stage_table_len(a.S) + 3) & ~3) + threadIdx.x;   // this thread's column: element c at s_in[c * BLOCK]
     const int tid = threadIdx.x;
-    for (int i = tid; i < stage_table_len(a.S); i += BLOCK) s_eps[i] = a.eps[i];
-    __syncthreads();
     const int64_t idx = (int64_t)blockIdx.x * BLOCK + tid;
-    if (idx >= a.B * a.ns) return;
-    const int64_t k = idx / a.B, b = idx % a.B;  // batch innermost: a warp shares k when 32 | B
-
-    Traj<T> tr;
-    load_traj(tr, [&](int j) { return __ldg(a.params + j * a.pB + b * a.pS); }, a.tauc, a.r0_km);
-    T x[NX];
-#pragma unroll
-    for (int j = 0; j < NX; ++j) x[j] = __ldg(a.X + (k * NX + j) * a.B + b);
-    Tangent<T, KIND, FAT, GROUPS> tg;
-    tg.init();
-
+    const bool live = idx < a.B * a.ns;
+    const int64_t k = live ? idx / a.B : 0, b = live ? idx % a.B : 0;  // batch innermost: a warp shares k when 32 | B
     const T *trow = a.tab + k * a.row * a.tB + b * a.tS;
     const T *crow = a.ctrl + k * a.nu * a.cB + b * a.cS;
+    const bool want_g = a.G != nullptr;
+    T *s_tab = s_in + (want_g ? 2 * NX : NX) * BLOCK, *s_ctl = s_tab + a.row * BLOCK;
+    if (live) {
+#pragma unroll
+        for (int j = 0; j < NX; ++j) __pipeline_memcpy_async(s_in + j * BLOCK, a.X + (k * NX + j) * a.B + b, sizeof(T));
+        if (want_g) {
+#pragma unroll
+            for (int j = 0; j < NX; ++j)
+                __pipeline_memcpy_async(s_in + (NX + j) * BLOCK, a.X + ((k + 1) * NX + j) * a.B + b, sizeof(T));
+        }
+        if (a.stage_tc) {
+            for (int c = 0; c < a.row; ++c) __pipeline_memcpy_async(s_tab + c * BLOCK, trow + c * a.tB, sizeof(T));
+            for (int c = 0; c < a.nu; ++c) __pipeline_memcpy_async(s_ctl + c * BLOCK, crow + c * a.cB, sizeof(T));
+        }
+    }
+    __pipeline_commit();
+    for (int i = tid; i < stage_table_len(a.S); i += BLOCK) s_eps[i] = a.eps[i];
+    Traj<T> tr;
+    load_traj(tr, [&](int j) { return __ldg(a.params + j * a.pB + b * a.pS); }, a.tauc, a.r0_km);
+    __pipeline_wait_prior(0);
+    __syncthreads();
+    if (!live) return;
+
+    T x[NX];
+#pragma unroll
+    for (int j = 0; j < NX; ++j) x[j] = s_in[j * BLOCK];
+    Tangent<T, KIND, FAT, GROUPS> tg;
+    tg.init(x);
+
     Interval<T, ND> iv;
-    interval_setup<T, KIND, FAT, GROUPS>(
-        tr, [&](int c) { return __ldg(trow + c * a.tB); }, [&](int c) { return __ldg(crow + c * a.cB); }, a.N,
-        a.tile_off, iv);
+    if (a.stage_tc)
+        interval_setup<T, KIND, FAT, GROUPS>(
+            tr, [&](int c) { return s_tab[c * BLOCK]; }, [&](int c) { return s_ctl[c * BLOCK]; }, a.N, a.tile_off, iv);
+    else
+        interval_setup<T, KIND, FAT, GROUPS>(
+            tr, [&](int c) { return __ldg(trow + c * a.tB); }, [&](int c) { return __ldg(crow + c * a.cB); }, a.N,
+            a.tile_off, iv);
     for (int i = 0; i < a.S; ++i)
         rk_step<T, KIND, FAT, GROUPS>(tr, iv, a.scheme, a.h, s_eps[2 * i], s_eps[2 * i + 1], s_eps[2 * i + 2],
                                       s_eps + 2 * a.S + 1 + 4 * i, x, tg);
@@ -249,7 +281,7 @@ __global__ void FES_LAUNCH_BOUNDS fes_shoot_kernel(const ShootArgs<T> a) {
 #pragma unroll
     for (int j = 0; j < NX; ++j) {
         if (a.Phi != nullptr) a.Phi[(k * NX + j) * a.B + b] = x[j];
-        if (a.G != nullptr) a.G[(k * NX + j) * a.B + b] = __ldg(a.X + ((k + 1) * NX + j) * a.B + b) - x[j];
+        if (want_g) a.G[(k * NX + j) * a.B + b] = s_in[(NX + j) * BLOCK] - x[j];
     }
     if constexpr (ND > 0) {
         if (a.J != nullptr) {
@@ -278,11 +310,20 @@ int launch_ivp_t(const IvpArgs<T> &a, cudaStream_t s) {
     return (int)cudaGetLastError();
 }
 
+// shared memory a shoot block may spend on staged table rows + controls (the node states are always staged): with 6
+// resident blocks this stays well inside the SM's 227 KB
+constexpr size_t SHOOT_STAGE_BUDGET = 24 * 1024;
+
 template <typename T, int KIND, bool FAT, int GROUPS>
-int launch_shoot_t(const ShootArgs<T> &a, cudaStream_t s) {
+int launch_shoot_t(const ShootArgs<T> &a0, cudaStream_t s) {
+    ShootArgs<T> a = a0;
     const int64_t total = a.B * a.ns;
     const unsigned grid = (unsigned)((total + BLOCK - 1) / BLOCK);
-    const size_t smem = ((stage_table_len(a.S) + 3) & ~3) * sizeof(T);
+    constexpr int NX = Dirs<KIND, FAT, GROUPS>::NX;
+    size_t vals = (size_t)(a.G != nullptr ? 2 * NX : NX);
+    a.stage_tc = (vals + a.row + a.nu) * BLOCK * sizeof(T) <= SHOOT_STAGE_BUDGET ? 1 : 0;
+    if (a.stage_tc) vals += (size_t)a.row + a.nu;
+    const size_t smem = (((stage_table_len(a.S) + 3) & ~3) + vals * BLOCK) * sizeof(T);
     fes_shoot_kernel<T, KIND, FAT, GROUPS><<<grid, BLOCK, smem, s>>>(a);
     return (int)cudaGetLastError();
 }

@@ -8,6 +8,8 @@
 #   bench32          bench.py --dtype f32
 #   strong1          the headline kernel on ONE GPU at the per-GPU batch of a strong-scaling split over 2 / 4 / 8 GPUs
 #   configs          scripts/bench_configs.py, fp64 and fp32
+#   margin           scripts/parity_margin.py: fp64 / fp32 errors against the oracle at 20, 100 and 300 s
+#   sweep            examples/sensitivity/truncation_sweep.py (15 150 points)
 #   scale<N>         torchrun bench.py --gpus N (needs gpurun --gpus N)
 #   ncu_list         launch list of the default bench command (after a plain run of it)
 #   ncu_full:<cfg>   ncu --set full of the top kernel of scripts/bench_configs.py --configs <cfg>  (2x0 = headline kernel)
@@ -39,6 +41,11 @@ for stage in "$@"; do
       timeout 900 python scripts/bench_configs.py --configs 1,2fwd,3,4,4b,4c,5,5pf > gpurun_out/configs_f64_$tag.jsonl 2> gpurun_out/configs_f64_$tag.err; echo "rc=$?"
       timeout 900 python scripts/bench_configs.py --configs 1,2fwd,2x0,3,4,4b,4c,5,5pf --dtype f32 > gpurun_out/configs_f32_$tag.jsonl 2> gpurun_out/configs_f32_$tag.err; echo "rc=$?"
       cut -c1-260 gpurun_out/configs_f64_$tag.jsonl gpurun_out/configs_f32_$tag.jsonl ;;
+    margin)
+      timeout 900 python scripts/parity_margin.py > gpurun_out/parity_margin_$tag.txt 2>&1; echo "margin rc=$?"; cat gpurun_out/parity_margin_$tag.txt ;;
+    sweep)
+      timeout 1200 python examples/sensitivity/truncation_sweep.py --out-dir gpurun_out > gpurun_out/truncation_sweep_$tag.txt 2>&1; echo "sweep rc=$?"
+      rm -f gpurun_out/truncation_*.pkl; cat gpurun_out/truncation_sweep_$tag.txt ;;
     scale*)
       n=${stage#scale}
       timeout 1200 python -m torch.distributed.run --nnodes=1 --nproc-per-node $n --master-addr 127.0.0.1 --master-port 29533 \

@@ -60,7 +60,7 @@ int ivp_cpu(const IvpArgs<T> &a) {
         T x[NX];
         for (int j = 0; j < NX; ++j) x[j] = a.x0[j * a.B + b];
         Tangent<T, KIND, FAT, GROUPS> tg;
-        tg.init();
+        tg.init(x);
         const bool tr_on = a.trace_mode != 0 && b < a.trace_B;
         auto put_state = [&](int64_t pt) {
             if (a.trace) for (int j = 0; j < NX; ++j) a.trace[(pt * NX + j) * a.trace_B + b] = x[j];
@@ -114,7 +114,7 @@ int shoot_cpu(const ShootArgs<T> &a) {
             T x[NX];
             for (int j = 0; j < NX; ++j) x[j] = a.X[(k * NX + j) * a.B + b];
             Tangent<T, KIND, FAT, GROUPS> tg;
-            tg.init();
+            tg.init(x);
             const T *trow = a.tab + k * a.row * a.tB + b * a.tS;
             const T *crow = a.ctrl + k * a.nu * a.cB + b * a.cS;
             Interval<T, ND> iv;

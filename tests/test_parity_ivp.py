@@ -192,6 +192,36 @@ def test_ivp_long_fatigue_protocol_matches_oracle(backend):
 
 
 @pytest.mark.parametrize("backend", BACKENDS, indirect=True)
+def test_ivp_fp32_mode_holds_over_a_long_protocol(backend):
+    """fp32 mode over 20 s of the fatigue protocol (6 600 RK4 steps).  What would break it in plain float arithmetic --
+    A, Tau1, Km accumulating increments of ~1e-4 of their size, and decay factors 1 - h/tau_fat that a float cannot hold --
+    is handled in the kernel (double accumulators for the three fatigue states, decays applied as exact small corrections,
+    fes_core.cuh): states stay at float rounding level, sensitivities well inside north_star's 1e-4."""
+    kind, fat = MODELS["ding2003_with_fatigue"]
+    T = 20
+    stim = [s + k / 33 for s in range(0, T, 2) for k in range(33)]
+    ns = 33 * T
+    win, _ = fes.stim_windows(stim, ns, T, 10)
+    B = 8
+    rng = np.random.default_rng(0)
+    params = fes.default_params(kind)[None] * np.concatenate([rng.uniform(0.8, 1.2, (B, 8)), np.ones((B, 6))], axis=1)
+    x0 = np.zeros((B, 5))
+    x0[:, 2], x0[:, 3], x0[:, 4] = params[:, 0], params[:, 2], params[:, 1]
+    f32 = torch.float32
+    p_t, x_t = torch.tensor(params.T.copy(), dtype=f32, device=backend), torch.tensor(x0.T.copy(), dtype=f32, device=backend)
+    res = fes.ivp(kind, fat, p_t, x_t, torch.tensor(win, device=backend), T / ns, n_steps=10, n_shooting=ns, trace="nodes",
+                  dirs=fes.FES_DIR_X0, sens_trace=True, dtype=f32)
+    # the oracle integrates the inputs the library was given (rounded to float), in double
+    ref = foc.ivp(kind, fat, 4, 10, ns, 10, T / ns, 0.020, 1.04, p_t.double().cpu().numpy().T.copy(),
+                  x_t.double().cpu().numpy().T.copy(), win[None], None, seed_x0=True, trace_B=B, sens_trace=True)
+    tr = np.transpose(res.trace.cpu().numpy(), (2, 0, 1))
+    st = np.transpose(res.sens_trace.cpu().numpy(), (3, 0, 1, 2))
+    for node in (17, 330, 611, 660):   # on-phase, end of an off-phase, last on-phase, end
+        assert entry_err(tr[:, node], ref["trace"][:, node], keep=(1,), tiny=1e-200) < 1e-5, node          # 10 x inside 1e-4
+        assert entry_err(st[:, node], ref["sens_trace"][:, node], keep=(1, 2), tiny=1e-200) < RTOL32, node
+
+
+@pytest.mark.parametrize("backend", BACKENDS, indirect=True)
 def test_ivp_argument_errors(backend):
     from cocofest_b200._lib import FesLibraryError
 
