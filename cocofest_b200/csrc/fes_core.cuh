@@ -333,6 +333,9 @@ FES_HD void interval_setup(const Traj<T> &tr, TF tab, CF ctl, int N, int tile_of
         T E = T(0);
         for (int i = 0; i < N; ++i) {
             const T wa = tab(2 + i), wb = tab(2 + N + i);
+            // a pad slot (-10 000 000, ding2003.py:394-397) has wa = wb = 0 exactly and adds exact zeros to every sum
+            // below: skipped, with its tanh (early nodes of a train are mostly pads)
+            if (wa == T(0) && wb == T(0)) continue;
             const T W = xfma(tr.r0m1, wb, wa);
             T lam = T(1), th = T(0), du = T(0);
             if constexpr (KIND == HMED2018) {

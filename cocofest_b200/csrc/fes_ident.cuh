@@ -51,8 +51,18 @@ struct IdentArgs {
 // The np + np(np+1)/2 running sums live in `acc` (element i at acc[i * stride]): on the device that is a
 // conflict-free column of shared memory per thread (stride = block size), which keeps 88 registers (Hmed, fp64)
 // out of the RK loop; they are touched once per node, i.e. once per S RK steps.  pc[j * pstride] = parameter j.
-template <typename T, int KIND>
-FES_HD void ident_eval(const IdentArgs<T> &a, int64_t b, const T *pc, int pstride, const T *eps, T &cost, T *acc, int stride) {
+// Where a candidate reads its window-table rows and controls from.  UNIT: a dense [ns][row] / [ns][nu] copy shared by all
+// candidates (the kernel stages it in shared memory when the tables and controls carry no batch axis): unit column stride
+// and 32-bit indices, which takes the 64-bit address arithmetic of the general strided layout out of the per-slot loop.
+template <typename T, bool UNIT>
+struct IdentRows {
+    const T *tab, *ctl;
+    int64_t t_node, t_col, c_node, c_col;  // UNIT: t_node = row, c_node = nu, column strides 1
+};
+
+template <typename T, int KIND, bool UNIT = false>
+FES_HD void ident_eval(const IdentArgs<T> &a, const IdentRows<T, UNIT> &rows, int64_t b, const T *pc, int pstride, const T *eps,
+                       T &cost, T *acc, int stride) {
     using I = IdentDims<KIND>;
     constexpr int NPK = I::NPK;
     Traj<T> tr;
@@ -93,11 +103,15 @@ FES_HD void ident_eval(const IdentArgs<T> &a, int64_t b, const T *pc, int pstrid
     };
     fold(0);
     for (int node = 0; node < a.ns; ++node) {
-        const T *trow = a.tab + (int64_t)node * a.row * a.tB + b * a.tS;
-        const T *crow = a.ctrl + (int64_t)node * a.nu * a.cB + b * a.cS;
         Interval<T, NPK> iv;
-        interval_setup<T, KIND, false, G_P>(
-            tr, [&](int c) { return trow[c * a.tB]; }, [&](int c) { return crow[c * a.cB]; }, a.N, 0, iv, lcp);
+        if constexpr (UNIT) {
+            const T *trow = rows.tab + node * (int)rows.t_node, *crow = rows.ctl + node * (int)rows.c_node;
+            interval_setup<T, KIND, false, G_P>(tr, [&](int c) { return trow[c]; }, [&](int c) { return crow[c]; }, a.N, 0, iv, lcp);
+        } else {
+            const T *trow = rows.tab + (int64_t)node * rows.t_node, *crow = rows.ctl + (int64_t)node * rows.c_node;
+            interval_setup<T, KIND, false, G_P>(
+                tr, [&](int c) { return trow[c * rows.t_col]; }, [&](int c) { return crow[c * rows.c_col]; }, a.N, 0, iv, lcp);
+        }
         for (int i = 0; i < a.S; ++i)
             rk_step<T, KIND, false, G_P>(tr, iv, a.scheme, a.h, eps[2 * i], eps[2 * i + 1], eps[2 * i + 2],
                                          eps + 2 * a.S + 1 + 4 * i, x, tg);
@@ -182,8 +196,14 @@ FES_HD bool ident_solve(GH gH, T lambda, int p_mask, T *delta) {
 template <int KIND>
 constexpr int ident_scratch() { return IdentDims<KIND>::NPK + IdentDims<KIND>::NH + NP; }
 
-template <typename T, int KIND>
-FES_HD void ident_candidate(const IdentArgs<T> &a, int64_t b, const T *eps, T *acc, int stride) {
+// the general (strided, per-candidate) row source of candidate b
+template <typename T>
+FES_HD IdentRows<T, false> ident_rows_strided(const IdentArgs<T> &a, int64_t b) {
+    return {a.tab + b * a.tS, a.ctrl + b * a.cS, (int64_t)a.row * a.tB, a.tB, (int64_t)a.nu * a.cB, a.cB};
+}
+
+template <typename T, int KIND, bool UNIT = false>
+FES_HD void ident_candidate(const IdentArgs<T> &a, const IdentRows<T, UNIT> &rows, int64_t b, const T *eps, T *acc, int stride) {
     using I = IdentDims<KIND>;
     constexpr int NPK = I::NPK;
     constexpr int NH = I::NH;
@@ -203,7 +223,7 @@ FES_HD void ident_candidate(const IdentArgs<T> &a, int64_t b, const T *eps, T *a
         });
     }
     T cost;
-    ident_eval<T, KIND>(a, b, pt, stride, eps, cost, acc, stride);
+    ident_eval<T, KIND, UNIT>(a, rows, b, pt, stride, eps, cost, acc, stride);
     auto publish = [&]() {  // the trial point becomes the current one
         a.cost[b] = cost;
         static_for<0, NPK + NH>([&](auto ic) {
@@ -250,7 +270,7 @@ FES_HD void ident_candidate(const IdentArgs<T> &a, int64_t b, const T *eps, T *a
             pt[j * stride] = v;  // rows that are not P-columns keep the current (= starting) value
         });
         if (!(step > T(0))) break;  // pinned on the box in every identified direction
-        ident_eval<T, KIND>(a, b, pt, stride, eps, cost, acc, stride);
+        ident_eval<T, KIND, UNIT>(a, rows, b, pt, stride, eps, cost, acc, stride);
         ++evals;
         if (cost < cur) {
             const T gain = cur - cost;
@@ -275,23 +295,44 @@ FES_HD void ident_candidate(const IdentArgs<T> &a, int64_t b, const T *eps, T *a
 #ifndef FES_IDENT_MIN_BLOCKS  // sweep knob (scripts/build_variants.sh)
 #define FES_IDENT_MIN_BLOCKS 6
 #endif
-template <typename T, int KIND>
+// STAGED: window tables and controls carry no batch axis (one stimulation train and one control sequence for all
+// candidates -- the identification case): the block copies them into shared memory once, [ns][row] and [ns][nu], and
+// every candidate reads its interval set-up from there.  Measured before (profiles/r01_ncu_ident_cfg4_ak_summary.tsv): 373
+// warp instructions executed per trajectory-step against 211 in the RK4 path -- the per-slot loop of the Hmed2018 set-up
+// (two table weights + one intensity per slot through 64-bit strided global addresses) was 43 % of the kernel.
+constexpr size_t IDENT_STAGE_BUDGET = 8 * 1024;   // bytes of staged rows per block, on top of the 30 KB of running sums
+
+template <typename T, int KIND, bool STAGED>
 __global__ void __launch_bounds__(BLOCK, FES_IDENT_MIN_BLOCKS) fes_ident_kernel(const IdentArgs<T> a) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     T *s_eps = reinterpret_cast<T *>(smem_raw);
     T *s_acc = s_eps + ((stage_table_len(a.S) + 3) & ~3);  // [ident_scratch][BLOCK]
+    T *s_tab = s_acc + ident_scratch<KIND>() * BLOCK;       // STAGED: [ns][row], then [ns][nu]
+    T *s_ctl = s_tab + a.ns * a.row;
     for (int i = threadIdx.x; i < stage_table_len(a.S); i += BLOCK) s_eps[i] = a.eps[i];
+    if constexpr (STAGED) {
+        for (int i = threadIdx.x; i < a.ns * a.row; i += BLOCK) s_tab[i] = a.tab[i];
+        for (int i = threadIdx.x; i < a.ns * a.nu; i += BLOCK) s_ctl[i] = a.ctrl[i];
+    }
     __syncthreads();
     const int64_t b = (int64_t)blockIdx.x * BLOCK + threadIdx.x;
     if (b >= a.B) return;
-    ident_candidate<T, KIND>(a, b, s_eps, s_acc + threadIdx.x, BLOCK);
+    if constexpr (STAGED) {
+        const IdentRows<T, true> rows = {s_tab, s_ctl, a.row, 1, a.nu, 1};
+        ident_candidate<T, KIND, true>(a, rows, b, s_eps, s_acc + threadIdx.x, BLOCK);
+    } else {
+        ident_candidate<T, KIND, false>(a, ident_rows_strided(a, b), b, s_eps, s_acc + threadIdx.x, BLOCK);
+    }
 }
 
 template <typename T, int KIND>
 int launch_ident_k(const IdentArgs<T> &a, cudaStream_t s) {
     const unsigned grid = (unsigned)((a.B + BLOCK - 1) / BLOCK);
-    const size_t smem = (((stage_table_len(a.S) + 3) & ~3) + (size_t)ident_scratch<KIND>() * BLOCK) * sizeof(T);
-    fes_ident_kernel<T, KIND><<<grid, BLOCK, smem, s>>>(a);
+    size_t smem = (((stage_table_len(a.S) + 3) & ~3) + (size_t)ident_scratch<KIND>() * BLOCK) * sizeof(T);
+    const size_t rows = (size_t)a.ns * (a.row + a.nu) * sizeof(T);
+    const bool staged = a.tS == 0 && (a.nu == 0 || a.cS == 0) && rows <= IDENT_STAGE_BUDGET;
+    if (staged) fes_ident_kernel<T, KIND, true><<<grid, BLOCK, smem + rows, s>>>(a);
+    else fes_ident_kernel<T, KIND, false><<<grid, BLOCK, smem, s>>>(a);
     return (int)cudaGetLastError();
 }
 

@@ -44,8 +44,8 @@ def load_sass_counts():
 
 def kernel_name(entry, dtype, kind, fatigue=None, groups=None):
     t = "double" if dtype in ("f64", torch.float64) else "float"
-    if entry == "ident":
-        return f"fes_ident_kernel<{t}, {KIND_NAME[kind]}>"
+    if entry == "ident":   # shared stimulation train and controls: the variant that stages them in shared memory
+        return f"fes_ident_kernel<{t}, {KIND_NAME[kind]}, staged>"
     bits = ((1, "X0"), (2, "U"), (4, "P"), (16, "PF"), (8, "W"))
     g = "|".join(n for b, n in bits if groups & b) or "0"
     return f"fes_{entry}_kernel<{t}, {KIND_NAME[kind]}, {'fatigue' if fatigue else 'no_fatigue'}, {g}>"

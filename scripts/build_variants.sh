@@ -9,6 +9,6 @@ for v in ${VARIANTS:-b128m0:128:0:0 b128m1:128:1:0 b128m3:128:3:0 b64m5:64:5:0 b
   [ "$minb" != "0" ] && extra="$extra -DFES_MIN_BLOCKS=$minb"
   [ "$maxr" != "0" ] && extra="$extra -maxrregcount=$maxr"
   [ -n "$defs" ] && extra="$extra -D$defs"
-  make -j8 BUILD=build/var_$name LIB=build/var_$name/libfes_b200.so EXTRA="$extra" > build/var_$name.log 2>&1 || { tail -5 build/var_$name.log; exit 1; }
+  make -j8 BUILD=build/var_$name LIB=build/var_$name/libfes_b200.so COUNTS=build/var_$name/sass_counts.json EXTRA="$extra" > build/var_$name.log 2>&1 || { tail -5 build/var_$name.log; exit 1; }
   echo "$name: $(grep -A3 'fes_ivp_kernelIdLi0ELb1ELi1E' build/var_$name/fes_inst_k0f1.ptxas.log | grep -o 'Used [0-9]* registers\|[0-9]* bytes spill stores' | tr '\n' ' ')"
 done

@@ -10,6 +10,8 @@
 #   configs          scripts/bench_configs.py, fp64 and fp32
 #   margin           scripts/parity_margin.py: fp64 / fp32 errors against the oracle at 20, 100 and 300 s
 #   sweep            examples/sensitivity/truncation_sweep.py (15 150 points)
+#   variants         every cocofest_b200/csrc/build/var_*/libfes_b200.so (scripts/build_variants.sh) through
+#                    scripts/bench_configs.py --configs $VCFG --dtype $VDT (defaults 2x0, f32), 60 s protocol
 #   scale<N>         torchrun bench.py --gpus N (needs gpurun --gpus N)
 #   ncu_list         launch list of the default bench command (after a plain run of it)
 #   ncu_full:<cfg>   ncu --set full of the top kernel of scripts/bench_configs.py --configs <cfg>  (2x0 = headline kernel)
@@ -46,6 +48,15 @@ for stage in "$@"; do
     sweep)
       timeout 1200 python examples/sensitivity/truncation_sweep.py --out-dir gpurun_out > gpurun_out/truncation_sweep_$tag.txt 2>&1; echo "sweep rc=$?"
       rm -f gpurun_out/truncation_*.pkl; cat gpurun_out/truncation_sweep_$tag.txt ;;
+    variants)
+      for lib in cocofest_b200/csrc/libfes_b200.so cocofest_b200/csrc/build/var_*/libfes_b200.so; do
+        echo "## $lib" | tee -a gpurun_out/variants_$tag.txt
+        FES_B200_LIB=$PWD/$lib timeout 600 python scripts/bench_configs.py --configs ${VCFG:-2x0} --dtype ${VDT:-f32} --t2 60 2>> gpurun_out/variants_$tag.err |
+          python -c "import sys, json
+for l in sys.stdin:
+    d = json.loads(l)
+    if 'config' in d: print(d['config'][:50], d['dtype'], '%.4e' % d['value'], '%.3f ms' % d['ms'], 'regs', (d.get('roofline') or {}).get('registers'))" | tee -a gpurun_out/variants_$tag.txt
+      done ;;
     scale*)
       n=${stage#scale}
       timeout 1200 python -m torch.distributed.run --nnodes=1 --nproc-per-node $n --master-addr 127.0.0.1 --master-port 29533 \

@@ -34,7 +34,9 @@ def pretty(sym):
     parts = ["double" if t == "d" else "float"]
     if kind is not None:
         parts.append(KIND.get(kind, kind))
-    if fat is not None:
+    if fat is not None and name == "fes_ident_kernel":   # fes_ident_kernel<T, KIND, STAGED>
+        parts.append("staged" if fat == "1" else "strided")
+    elif fat is not None:
         parts.append("fatigue" if fat == "1" else "no_fatigue")
     if groups is not None:
         g = int(groups)

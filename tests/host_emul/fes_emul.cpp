@@ -233,9 +233,18 @@ int ident_impl(const FesDesc *d, const FesIdentBuffers *b, const FesIdentOptions
     T acc[8 + 36 + FES_NP];  // per-candidate scratch (ident_scratch<KIND>(), shared memory on the device)
     for (int64_t i = 0; i < a.B; ++i) {
         switch (d->model_kind) {
-            case 0: ident_candidate<T, 0>(a, i, a.eps, acc, 1); break;
-            case 1: ident_candidate<T, 1>(a, i, a.eps, acc, 1); break;
-            default: ident_candidate<T, 2>(a, i, a.eps, acc, 1); break;
+            case 0: ident_candidate<T, 0>(a, ident_rows_strided(a, i), i, a.eps, acc, 1); break;
+            case 1: ident_candidate<T, 1>(a, ident_rows_strided(a, i), i, a.eps, acc, 1); break;
+            default:
+                // tables and controls without batch axis: the dense unit-stride row source the CUDA kernel stages in
+                // shared memory (fes_ident_kernel<.., STAGED>), read here straight from the workspace
+                if (a.tS == 0 && a.cS == 0) {
+                    const IdentRows<T, true> rows = {a.tab, a.ctrl, a.row, 1, a.nu, 1};
+                    ident_candidate<T, 2, true>(a, rows, i, a.eps, acc, 1);
+                } else {
+                    ident_candidate<T, 2>(a, ident_rows_strided(a, i), i, a.eps, acc, 1);
+                }
+                break;
         }
     }
     return 0;
