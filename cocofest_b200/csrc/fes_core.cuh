@@ -193,7 +193,15 @@ FES_HD double xfma(double a, double b, double c) { return fma(a, b, c); }
 FES_HD float xfma(float a, float b, float c) { return fmaf(a, b, c); }
 FES_HD double xexp(double a) { return exp(a); }
 FES_HD float xexp(float a) { return expf(a); }
-FES_HD double xtanh(double a) { return tanh(a); }
+// tanh without the branch of the library version (|x| < 0.55: polynomial, else exp): lanes of a warp hold different
+// candidates, so both sides were executed (~95 instructions per window slot).  th = (1 - t)/(1 + t), t = exp(-2|x|), has an
+// ABSOLUTE error of ~1e-16 (near 0 the subtraction 1 - t is exact, t itself carries the rounding), which is what its uses
+// need: th is only ever added to cr ~ 0.8 (lambda_i_calculation, hmed2018.py:179) or squared into 1 - th^2.
+FES_HD double xrcp(double x);
+FES_HD double xtanh(double a) {
+    const double t = exp(-2.0 * fabs(a));
+    return copysign((1.0 - t) * xrcp(1.0 + t), a);
+}
 FES_HD float xtanh(float a) { return tanhf(a); }
 FES_HD double xsqrt(double a) { return sqrt(a); }
 FES_HD float xsqrt(float a) { return sqrtf(a); }

@@ -221,14 +221,17 @@ __global__ void FES_LAUNCH_BOUNDS fes_ivp_kernel(const IvpArgs<T> a) {
 }
 
 // ---------------------------------------------------------------------------------------------
-// One work item = ONE interval of S steps of one scenario: ~3000 issued instructions.  With one short-lived thread per item
-// (round 1) the fp64 pipe was 70 % active: every item exposed the latency of its own input loads (under the register cap they
-// sink next to their first use: four dependent round trips, long_scoreboard 1.33 cycles per issue,
-// profiles/r01_ncu_shoot_cfg5_ai_summary.tsv) and paid block launch / drain for ~25 000 cycles of work.  Now the grid is
-// PERSISTENT (as many blocks as are resident at once, each thread strides over the items) and the inputs of the NEXT item
-// (node state, next node state, per-scenario parameters, and the table row + controls when they fit) are copied global ->
-// shared with cp.async (LDGSTS, no registers) into the other half of a double buffer while the current item integrates;
-// the integration reads its inputs from the thread's own shared-memory column [value][thread] (conflict-free).
+// Every thread integrates ONE interval of S steps, so the latency of its input loads is paid once per ~3000 issued
+// instructions instead of once per trajectory: left to the compiler (under the register cap the loads sink next to their
+// first use) four dependent round trips to HBM were exposed per thread -- long_scoreboard 1.33 cycles per issue, fp64 pipe
+// 70 % active (profiles/r01_ncu_shoot_cfg5_ai_summary.tsv).  Here the thread's inputs (node state, next node state, and the
+// table row + controls when they fit) are copied global -> shared with cp.async (LDGSTS, no registers) as the first thing
+// the thread does, all in flight at once and overlapped with the stage-table load and the parameter set-up; the
+// integration then reads them from its own shared-memory column [value][thread] (conflict-free).  Measured on config 5:
+// 0.539 -> 0.522 ms.  A PERSISTENT grid with the next item's inputs prefetched into a double buffer was tried on top of
+// this and lost (0.627 ms, profiles/r02_tune_persistent_shoot_d_f64.jsonl): identical work items keep the resident warps in
+// phase, so their set-up / store phases no longer overlap other warps' RK phases; the hardware's own staggered block launch
+// does that better.
 template <typename T, int KIND, bool FAT, int GROUPS>
 __global__ void FES_LAUNCH_BOUNDS fes_shoot_kernel(const ShootArgs<T> a) {
     using D = Dirs<KIND, FAT, GROUPS>;
@@ -236,86 +239,66 @@ __global__ void FES_LAUNCH_BOUNDS fes_shoot_kernel(const ShootArgs<T> a) {
     constexpr int ND = D::ND;
     extern __shared__ __align__(16) unsigned char smem_raw[];
     T *s_eps = reinterpret_cast<T *>(smem_raw);
+    T *s_in = s_eps + ((stage_table_len(a.S) + 3) & ~3) + threadIdx.x;   // this thread's column: element c at s_in[c * BLOCK]
     const int tid = threadIdx.x;
-    const bool want_g = a.G != nullptr, own_p = a.pS != 0;
-    // staged values of one item, per thread: x_k [NX] | x_{k+1} [NX] (defects) | params [NP] (per scenario) | row | controls
-    const int o_p = want_g ? 2 * NX : NX, o_t = o_p + (own_p ? NP : 0), o_c = o_t + (a.stage_tc ? a.row : 0);
-    const int vals = o_c + (a.stage_tc ? a.nu : 0);
-    T *s_buf = s_eps + ((stage_table_len(a.S) + 3) & ~3) + tid;   // buffer q, element c: s_buf[(q * vals + c) * BLOCK]
-    const int64_t total = a.B * a.ns, stride = (int64_t)gridDim.x * BLOCK;
-
-    auto prefetch = [&](int64_t item, int q) {
-        if (item < total) {
-            const int64_t k = item / a.B, b = item % a.B;  // batch innermost: a warp shares k when 32 | B
-            T *dst = s_buf + (int64_t)q * vals * BLOCK;
+    const int64_t idx = (int64_t)blockIdx.x * BLOCK + tid;
+    const bool live = idx < a.B * a.ns;
+    const int64_t k = live ? idx / a.B : 0, b = live ? idx % a.B : 0;  // batch innermost: a warp shares k when 32 | B
+    const T *trow = a.tab + k * a.row * a.tB + b * a.tS;
+    const T *crow = a.ctrl + k * a.nu * a.cB + b * a.cS;
+    const bool want_g = a.G != nullptr;
+    T *s_tab = s_in + (want_g ? 2 * NX : NX) * BLOCK, *s_ctl = s_tab + a.row * BLOCK;
+    if (live) {
 #pragma unroll
-            for (int j = 0; j < NX; ++j) __pipeline_memcpy_async(dst + j * BLOCK, a.X + (k * NX + j) * a.B + b, sizeof(T));
-            if (want_g) {
+        for (int j = 0; j < NX; ++j) __pipeline_memcpy_async(s_in + j * BLOCK, a.X + (k * NX + j) * a.B + b, sizeof(T));
+        if (want_g) {
 #pragma unroll
-                for (int j = 0; j < NX; ++j)
-                    __pipeline_memcpy_async(dst + (NX + j) * BLOCK, a.X + ((k + 1) * NX + j) * a.B + b, sizeof(T));
-            }
-            if (own_p) {
-#pragma unroll
-                for (int j = 0; j < NP; ++j) __pipeline_memcpy_async(dst + (o_p + j) * BLOCK, a.params + j * a.pB + b, sizeof(T));
-            }
-            if (a.stage_tc) {
-                const T *trow = a.tab + k * a.row * a.tB + b * a.tS, *crow = a.ctrl + k * a.nu * a.cB + b * a.cS;
-                for (int c = 0; c < a.row; ++c) __pipeline_memcpy_async(dst + (o_t + c) * BLOCK, trow + c * a.tB, sizeof(T));
-                for (int c = 0; c < a.nu; ++c) __pipeline_memcpy_async(dst + (o_c + c) * BLOCK, crow + c * a.cB, sizeof(T));
-            }
+            for (int j = 0; j < NX; ++j)
+                __pipeline_memcpy_async(s_in + (NX + j) * BLOCK, a.X + ((k + 1) * NX + j) * a.B + b, sizeof(T));
         }
-        __pipeline_commit();  // an empty group when there is nothing left: the wait below counts groups
-    };
-
-    int64_t item = (int64_t)blockIdx.x * BLOCK + tid;
-    prefetch(item, 0);
+        if (a.stage_tc) {
+            for (int c = 0; c < a.row; ++c) __pipeline_memcpy_async(s_tab + c * BLOCK, trow + c * a.tB, sizeof(T));
+            for (int c = 0; c < a.nu; ++c) __pipeline_memcpy_async(s_ctl + c * BLOCK, crow + c * a.cB, sizeof(T));
+        }
+    }
+    __pipeline_commit();
     for (int i = tid; i < stage_table_len(a.S); i += BLOCK) s_eps[i] = a.eps[i];
     Traj<T> tr;
-    if (!own_p) load_traj(tr, [&](int j) { return __ldg(a.params + j); }, a.tauc, a.r0_km);  // one parameter set for all
+    load_traj(tr, [&](int j) { return __ldg(a.params + j * a.pB + b * a.pS); }, a.tauc, a.r0_km);
+    __pipeline_wait_prior(0);
     __syncthreads();
+    if (!live) return;
 
-    for (int q = 0; item < total; item += stride, q ^= 1) {
-        prefetch(item + stride, q ^ 1);
-        __pipeline_wait_prior(1);  // everything but the group just committed has landed: this item's inputs
-        const int64_t k = item / a.B, b = item % a.B;
-        const T *in = s_buf + (int64_t)q * vals * BLOCK;
-        if (own_p) load_traj(tr, [&](int j) { return in[(o_p + j) * BLOCK]; }, a.tauc, a.r0_km);
-        T x[NX];
+    T x[NX];
 #pragma unroll
-        for (int j = 0; j < NX; ++j) x[j] = in[j * BLOCK];
-        Tangent<T, KIND, FAT, GROUPS> tg;
-        tg.init(x);
+    for (int j = 0; j < NX; ++j) x[j] = s_in[j * BLOCK];
+    Tangent<T, KIND, FAT, GROUPS> tg;
+    tg.init(x);
 
-        Interval<T, ND> iv;
-        if (a.stage_tc) {
-            const T *s_tab = in + o_t * BLOCK, *s_ctl = in + o_c * BLOCK;
-            interval_setup<T, KIND, FAT, GROUPS>(
-                tr, [&](int c) { return s_tab[c * BLOCK]; }, [&](int c) { return s_ctl[c * BLOCK]; }, a.N, a.tile_off, iv);
-        } else {
-            const T *trow = a.tab + k * a.row * a.tB + b * a.tS, *crow = a.ctrl + k * a.nu * a.cB + b * a.cS;
-            interval_setup<T, KIND, FAT, GROUPS>(
-                tr, [&](int c) { return __ldg(trow + c * a.tB); }, [&](int c) { return __ldg(crow + c * a.cB); }, a.N,
-                a.tile_off, iv);
-        }
-        for (int i = 0; i < a.S; ++i)
-            rk_step<T, KIND, FAT, GROUPS>(tr, iv, a.scheme, a.h, s_eps[2 * i], s_eps[2 * i + 1], s_eps[2 * i + 2],
-                                          s_eps + 2 * a.S + 1 + 4 * i, x, tg);
+    Interval<T, ND> iv;
+    if (a.stage_tc)
+        interval_setup<T, KIND, FAT, GROUPS>(
+            tr, [&](int c) { return s_tab[c * BLOCK]; }, [&](int c) { return s_ctl[c * BLOCK]; }, a.N, a.tile_off, iv);
+    else
+        interval_setup<T, KIND, FAT, GROUPS>(
+            tr, [&](int c) { return __ldg(trow + c * a.tB); }, [&](int c) { return __ldg(crow + c * a.cB); }, a.N,
+            a.tile_off, iv);
+    for (int i = 0; i < a.S; ++i)
+        rk_step<T, KIND, FAT, GROUPS>(tr, iv, a.scheme, a.h, s_eps[2 * i], s_eps[2 * i + 1], s_eps[2 * i + 2],
+                                      s_eps + 2 * a.S + 1 + 4 * i, x, tg);
 
 #pragma unroll
-        for (int j = 0; j < NX; ++j) {
-            if (a.Phi != nullptr) a.Phi[(k * NX + j) * a.B + b] = x[j];
-            if (want_g) a.G[(k * NX + j) * a.B + b] = in[(NX + j) * BLOCK] - x[j];
-        }
-        if constexpr (ND > 0) {
-            if (a.J != nullptr) {
-                static_for<0, ND>([&](auto ic) {
-                    constexpr int d = decltype(ic)::value;
+    for (int j = 0; j < NX; ++j) {
+        if (a.Phi != nullptr) a.Phi[(k * NX + j) * a.B + b] = x[j];
+        if (want_g) a.G[(k * NX + j) * a.B + b] = s_in[(NX + j) * BLOCK] - x[j];
+    }
+    if constexpr (ND > 0) {
+        if (a.J != nullptr) {
+            static_for<0, ND>([&](auto ic) {
+                constexpr int d = decltype(ic)::value;
 #pragma unroll
-                    for (int j = 0; j < NX; ++j)
-                        a.J[((k * NX + j) * a.j_cols + a.j_col0 + d) * a.B + b] = tg.template get<d>(tr, j);
-                });
-            }
+                for (int j = 0; j < NX; ++j) a.J[((k * NX + j) * a.j_cols + a.j_col0 + d) * a.B + b] = tg.template get<d>(tr, j);
+            });
         }
     }
 }
@@ -336,31 +319,20 @@ int launch_ivp_t(const IvpArgs<T> &a, cudaStream_t s) {
     return (int)cudaGetLastError();
 }
 
-// shared memory one half of a shoot block's double buffer may spend on staged table rows + controls (node states and
-// per-scenario parameters are always staged): two halves x 6 resident blocks stay well inside the SM's 227 KB
-constexpr size_t SHOOT_STAGE_BUDGET = 14 * 1024;
+// shared memory a shoot block may spend on staged table rows + controls (the node states are always staged): with 6
+// resident blocks this stays well inside the SM's 227 KB
+constexpr size_t SHOOT_STAGE_BUDGET = 24 * 1024;
 
 template <typename T, int KIND, bool FAT, int GROUPS>
 int launch_shoot_t(const ShootArgs<T> &a0, cudaStream_t s) {
     ShootArgs<T> a = a0;
     const int64_t total = a.B * a.ns;
+    const unsigned grid = (unsigned)((total + BLOCK - 1) / BLOCK);
     constexpr int NX = Dirs<KIND, FAT, GROUPS>::NX;
-    size_t vals = (size_t)(a.G != nullptr ? 2 * NX : NX) + (a.pS != 0 ? NP : 0);
+    size_t vals = (size_t)(a.G != nullptr ? 2 * NX : NX);
     a.stage_tc = (vals + a.row + a.nu) * BLOCK * sizeof(T) <= SHOOT_STAGE_BUDGET ? 1 : 0;
     if (a.stage_tc) vals += (size_t)a.row + a.nu;
-    const size_t smem = (((stage_table_len(a.S) + 3) & ~3) + 2 * vals * BLOCK) * sizeof(T);
-    // persistent grid: the blocks that are resident at once (occupancy of THIS instantiation with THIS shared memory)
-    static int sms = 0;
-    if (sms == 0) {
-        int dev = 0;
-        cudaGetDevice(&dev);
-        cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
-    }
-    int per_sm = 0;
-    cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, fes_shoot_kernel<T, KIND, FAT, GROUPS>, BLOCK, smem);
-    if (per_sm < 1) per_sm = 1;
-    const int64_t need = (total + BLOCK - 1) / BLOCK;
-    const unsigned grid = (unsigned)std::min<int64_t>(need, (int64_t)sms * per_sm);
+    const size_t smem = (((stage_table_len(a.S) + 3) & ~3) + vals * BLOCK) * sizeof(T);
     fes_shoot_kernel<T, KIND, FAT, GROUPS><<<grid, BLOCK, smem, s>>>(a);
     return (int)cudaGetLastError();
 }
