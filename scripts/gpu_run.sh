@@ -10,6 +10,7 @@
 #   configs          scripts/bench_configs.py, fp64 and fp32
 #   margin           scripts/parity_margin.py: fp64 / fp32 errors against the oracle at 20, 100 and 300 s
 #   sweep            examples/sensitivity/truncation_sweep.py (15 150 points)
+#   probe            scripts/probes/ffma_operands (built here: nvcc -O3 -o scripts/probes/ffma_operands scripts/probes/ffma_operands.cu)
 #   variants         every cocofest_b200/csrc/build/var_*/libfes_b200.so (scripts/build_variants.sh) through
 #                    scripts/bench_configs.py --configs $VCFG --dtype $VDT (defaults 2x0, f32), 60 s protocol
 #   scale<N>         torchrun bench.py --gpus N (needs gpurun --gpus N)
@@ -48,6 +49,8 @@ for stage in "$@"; do
     sweep)
       timeout 1200 python examples/sensitivity/truncation_sweep.py --out-dir gpurun_out > gpurun_out/truncation_sweep_$tag.txt 2>&1; echo "sweep rc=$?"
       rm -f gpurun_out/truncation_*.pkl; cat gpurun_out/truncation_sweep_$tag.txt ;;
+    probe)
+      timeout 300 scripts/probes/ffma_operands > gpurun_out/probe_ffma_operands_$tag.txt 2>&1; echo "probe rc=$?"; cat gpurun_out/probe_ffma_operands_$tag.txt ;;
     variants)
       for lib in cocofest_b200/csrc/libfes_b200.so cocofest_b200/csrc/build/var_*/libfes_b200.so; do
         echo "## $lib" | tee -a gpurun_out/variants_$tag.txt
