@@ -78,10 +78,12 @@ FES_HD void ident_eval(const IdentArgs<T> &a, const IdentRows<T, UNIT> &rows, in
     [[maybe_unused]] LamCache<T> lc;
     // measured (profiles/r01_tune_ident_lamcache_x.txt): +2.5 % for the plain evaluation, -2.4 % inside the LM loop,
     // where the cache would be refilled at every evaluation (bs and Is move) next to ~1.3 KB of register spills
+#ifndef FES_NO_LAMCACHE
     if (KIND == HMED2018 && a.max_iter == 0) {
         lc.reset(a.N);
         lcp = &lc;
     }
+#endif
     cost = T(0);
     T *g = acc, *H = acc + NPK * stride;
     static_for<0, NPK + I::NH>([&](auto ic) { acc[decltype(ic)::value * stride] = T(0); });

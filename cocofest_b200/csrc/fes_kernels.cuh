@@ -141,10 +141,12 @@ __global__ void FES_LAUNCH_BOUNDS fes_ivp_kernel(const IvpArgs<T> a) {
     tg.init(x);
     LamCache<T> *lcp = nullptr;
     [[maybe_unused]] LamCache<T> lc;
+#ifndef FES_NO_LAMCACHE  // sweep knob: with the branch-free tanh the cache of the previous interval's tanh may not pay any more
     if constexpr (KIND == HMED2018) {
         lc.reset(a.N);
         lcp = &lc;
     }
+#endif
 
     const bool tr_on = live && a.trace_mode != 0 && b < a.trace_B;
     auto put_state = [&](int64_t pt) {

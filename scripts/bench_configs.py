@@ -116,7 +116,7 @@ def record(name, kernel, units, ms, out_bytes, in_bytes, dtype, counts, peaks, h
 
 
 def run_configs(wanted, dev, dtype="f64", steps=3, warmup=3, scale=1.0, flush=None, t2=300):
-    """Runs the configurations in `wanted` (strings: "1", "2fwd", "2x0", "3", "4", "4b", "4c", "5", "5pf") on `dev`; returns
+    """Runs the configurations in `wanted` (strings: "1", "2fwd", "2x0", "2pf", "3", "4", "4b", "4c", "5", "5pf") on `dev`; returns
     (records, meta)."""
     dt_t = torch.float64 if dtype == "f64" else torch.float32
     esz = 8 if dtype == "f64" else 4
@@ -151,7 +151,7 @@ def run_configs(wanted, dev, dtype="f64", steps=3, warmup=3, scale=1.0, flush=No
             {"batch": B, "n_shooting": ns, "F_end": float(out.x_final[1, 0])})
         del out, x0
 
-    for tag, dirs in (("2fwd", 0), ("2x0", fes.FES_DIR_X0)):
+    for tag, dirs in (("2fwd", 0), ("2x0", fes.FES_DIR_X0), ("2pf", fes.FES_DIR_P | fes.FES_DIR_PF)):
         if tag not in wanted:
             continue
         # BASELINE configs[1]: forward only (as the config line states it) / with d x/d x0 (the headline, e.g. in fp32)
@@ -166,7 +166,8 @@ def run_configs(wanted, dev, dtype="f64", steps=3, warmup=3, scale=1.0, flush=No
                              trace_batch=1024, dirs=dirs, dtype=dt_t)
         out, ms = timed(fn, max(1, min(steps, 2)), max(1, min(warmup, 2)), flush)
         ob = (out.trace.numel() + out.x_final.numel() + (out.sens_final.numel() if dirs else 0)) * esz
-        add(f"2: Ding2003+fatigue 33 Hz protocol, {T} s, 1M trajectories, " + ("with d x/d x0" if dirs else "forward only"),
+        what = {0: "forward only", fes.FES_DIR_X0: "with d x/d x0"}.get(dirs, "with d x/d (4 model + 4 fatigue parameters)")
+        add(f"2: Ding2003+fatigue 33 Hz protocol, {T} s, 1M trajectories, " + what,
             kernel_name("ivp", dtype, fes.FES_DING2003, True, dirs), B * ns * S, ms, ob, (p.numel() + x0.numel()) * esz, dtype,
             {"batch": B, "n_shooting": ns, "final_time_s": T, "F_end_mean": float(out.x_final[1].mean())})
         del out, p, x0

@@ -6,6 +6,8 @@
 //   reg3     a[j] = fma(a[j], b[j'], c[j''])   three distinct registers per FFMA
 //   reg3x2   the same on float2 pairs with fma.rn.f32x2
 //   mix      reg3 with every third FFMA replaced by FMUL + FADD on distinct registers (the kernels' 121 : 95 : 26 mix)
+//   mixfma   the same arithmetic with the multiply written as fma(a, b, -0) and the add as fma(a, 1, c): FFMA only
+//   mulonly / addonly   all FMUL, all FADD (which of the two costs the rate)
 #include <cstdio>
 #include <cuda_runtime.h>
 
@@ -18,6 +20,12 @@ __device__ __forceinline__ float2 fma2(float2 a, float2 b, float2 c) {
         "fma.rn.f32x2 rd, ra, rb, rc;\n\t"
         "mov.b64 {%0, %1}, rd;}"
         : "=f"(d.x), "=f"(d.y) : "f"(a.x), "f"(a.y), "f"(b.x), "f"(b.y), "f"(c.x), "f"(c.y));
+    return d;
+}
+
+__device__ __forceinline__ float fma_asm(float a, float b, float c) {
+    float d;
+    asm("fma.rn.f32 %0, %1, %2, %3;" : "=f"(d) : "f"(a), "f"(b), "f"(c));
     return d;
 }
 
@@ -36,9 +44,15 @@ __global__ void probe(float *out, int iters, float seed) {
             if (MODE == 0) a[j] = fmaf(a[j], 0.9999f, 1e-7f);
             if (MODE == 1) a[j] = fmaf(a[j], b[(j + 1) % K], c[(j + 5) % K]);
             if (MODE == 3) {
-                if (j % 3 == 2) a[j] = a[j] * b[(j + 1) % K] + 0.f, a[j] = __fadd_rn(a[j], c[(j + 5) % K]);
+                if (j % 3 == 2) a[j] = __fmul_rn(a[j], b[(j + 1) % K]), a[j] = __fadd_rn(a[j], c[(j + 5) % K]);
                 else a[j] = fmaf(a[j], b[(j + 1) % K], c[(j + 5) % K]);
             }
+            if (MODE == 4) {
+                if (j % 3 == 2) a[j] = fma_asm(a[j], b[(j + 1) % K], -0.0f), a[j] = fma_asm(a[j], 1.0f, c[(j + 5) % K]);
+                else a[j] = fmaf(a[j], b[(j + 1) % K], c[(j + 5) % K]);
+            }
+            if (MODE == 5) a[j] = __fmul_rn(a[j], b[(j + 1) % K]);
+            if (MODE == 6) a[j] = __fadd_rn(a[j], c[(j + 5) % K]);
         }
         if (MODE == 2) {
 #pragma unroll
@@ -84,11 +98,14 @@ int main() {
     cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, 0);
     float *out;
     cudaMalloc(&out, 4);
-    for (int bps : {2, 4, 8}) {
+    for (int bps : {2, 8}) {
         run<0>("const2", sms, 256, bps, out);
         run<1>("reg3", sms, 256, bps, out);
         run<2>("reg3x2", sms, 256, bps, out);
         run<3>("mix", sms, 256, bps, out);
+        run<4>("mixfma", sms, 256, bps, out);
+        run<5>("mulonly", sms, 256, bps, out);
+        run<6>("addonly", sms, 256, bps, out);
     }
     cudaError_t e = cudaDeviceSynchronize();
     printf("status %s\n", cudaGetErrorString(e));
