@@ -24,7 +24,7 @@
 
 namespace fes {
 
-// launch shape: tuned on a B200 (scripts/build_variants.sh + scripts/gpu_round1_d.sh, profiles/r01_tune_ivp_d.txt);
+// launch shape: tuned on a B200 (scripts/build_variants.sh + the variants stage of scripts/gpu_run.sh, profiles/r01_tune_ivp_d.txt);
 // overridable for that sweep only
 #ifndef FES_BLOCK
 #define FES_BLOCK 64

@@ -46,9 +46,11 @@ def padded_windows(points, final_time=1.0):
     ns = points[0][3]
     n_max = max(j for _, j, _, _ in points)
     win = np.full((ns + 1, n_max, len(points)), float(fes.PAD_TIME))
-    for b, (_, j, stim, _) in enumerate(points):
-        w, _ = fes.stim_windows(stim, ns, final_time, j)
-        win[:, n_max - j:, b] = w
+    widest = {}   # the window of truncation j is the last j slots of the train's widest window: one builder call per train
+    for b, (i, j, stim, _) in enumerate(points):
+        if i not in widest:
+            widest[i] = fes.stim_windows(stim, ns, final_time, max(q[1] for q in points if q[0] == i))[0]
+        win[:, n_max - j:, b] = widest[i][:, widest[i].shape[1] - j:]
     return win
 
 
