@@ -126,12 +126,6 @@ constexpr bool dir_rest(int c) { return c == D_A_REST || c == D_TAU1_REST || c =
 constexpr bool dir_alpha(int c) { return c == D_ALPHA_A || c == D_ALPHA_TAU1 || c == D_ALPHA_KM; }
 constexpr bool dir_own_m(int c) { return c == D_TAU_FAT; }  // mA, mT1, mKm kept in V[d][0], V[d][3], V[d][4]
 template <class D>
-constexpr bool dirs_all_reduced() {
-    for (int d = 0; d < D::ND; ++d)
-        if (!dir_reduced(D::NX == 5, D::code(d))) return false;
-    return true;
-}
-template <class D>
 constexpr bool dirs_any_forced_cn() {
     for (int d = 0; d < D::ND; ++d)
         if (dir_forced_cn(D::code(d))) return true;
@@ -393,7 +387,7 @@ FES_HD void interval_setup(const Traj<T> &tr, TF tab, CF ctl, int N, int tile_of
 // ---- one RK stage of the nominal trajectory ------------------------------------------------
 template <typename T>
 struct Stage {  // the non-trivial entries of d f / d (x, params) at a stage point
-    T cF, cCn, cKm, cT1, cA, cT2, cG, Fs, dA, dT1, dKm;
+    T cF, cCn, cKm, cT1, cA, cT2, cG, dA, dT1, dKm;
     T cW;  // fatigue: d F' / d W = cA alpha_a + cT1 alpha_tau1 + cKm alpha_km  (reduced columns)
 };
 
@@ -428,7 +422,6 @@ FES_HD void nominal_rhs(const Traj<T> &tr, T Ee, T g, const T *x, T *k, Stage<T>
         st.cA = (KIND == DING2007) ? q * g : q;
         st.cT2 = ct1 * q;
         st.cG = A * q;
-        st.Fs = f;
         if constexpr (FAT) {
             st.cW = xfma(st.cA, tr.alpha_a, xfma(st.cT1, tr.alpha_tau1, st.cKm * tr.alpha_km));
             st.dA = (A - tr.a_rest) * tr.kappa2;   // d/d tau_fat of -(A - A_rest)/tau_fat
@@ -438,11 +431,12 @@ FES_HD void nominal_rhs(const Traj<T> &tr, T Ee, T g, const T *x, T *k, Stage<T>
     }
 }
 
-// ---- one RK stage of one tangent column -----------------------------------------------------
+// ---- one RK stage of one tangent column of a TWO-STATE model (Cn, F) ---------------------------
 // pc_dl = cCn dl_s, pc_psi = cCn psi_s (forced-Cn columns, see dir_forced_cn; S0: first stage, psi_0 = 0);
 // v[0] of such a column is its Cn component at the step start and k[0] is not produced.
 // SH: the forced Cn components of this direction set use the shared modes.
-template <typename T, int KIND, bool FAT, int CODE, bool S0, bool SH>
+// (Every column of a fatigue model goes through column_rhs_red below.)
+template <typename T, int KIND, int CODE, bool S0, bool SH>
 FES_HD void column_rhs(const Traj<T> &tr, const Stage<T> &st, T eps, T sE, T dg, T pc_dl, T pc_psi, const T *v, T *k) {
     constexpr bool OWN = CODE == D_CN0 || (dir_forced_cn(CODE) && !SH);  // integrates its own Cn component
     if constexpr (CODE == D_CN0) k[0] = -(v[0] * tr.inv_tauc);
@@ -454,37 +448,12 @@ FES_HD void column_rhs(const Traj<T> &tr, const Stage<T> &st, T eps, T sE, T dg,
         kf = xfma(pc_dl, v[0], kf);
         if constexpr (!S0) kf = xfma(pc_psi, sE, kf);
     }
-    if constexpr (FAT) {
-        kf = xfma(st.cA, v[2], kf);
-        kf = xfma(st.cT1, v[3], kf);
-        kf = xfma(st.cKm, v[4], kf);
-    } else {
-        if constexpr (CODE == D_A_REST) kf += st.cA;
-        if constexpr (CODE == D_TAU1_REST) kf += st.cT1;
-        if constexpr (CODE == D_KM_REST) kf += st.cKm;
-    }
+    if constexpr (CODE == D_A_REST) kf += st.cA;
+    if constexpr (CODE == D_TAU1_REST) kf += st.cT1;
+    if constexpr (CODE == D_KM_REST) kf += st.cKm;
     if constexpr (CODE == D_TAU2) kf += st.cT2;
     if constexpr (dir_has_dg(CODE)) kf = xfma(st.cG, dg, kf);
     k[1] = kf;
-    if constexpr (FAT) {
-        T ka = xfma(tr.alpha_a, v[1], -(tr.kappa * v[2]));
-        T kt = xfma(tr.alpha_tau1, v[1], -(tr.kappa * v[3]));
-        T kk = xfma(tr.alpha_km, v[1], -(tr.kappa * v[4]));
-        if constexpr (CODE == D_A_REST) ka += tr.kappa;
-        if constexpr (CODE == D_TAU1_REST) kt += tr.kappa;
-        if constexpr (CODE == D_KM_REST) kk += tr.kappa;
-        if constexpr (CODE == D_ALPHA_A) ka += st.Fs;
-        if constexpr (CODE == D_ALPHA_TAU1) kt += st.Fs;
-        if constexpr (CODE == D_ALPHA_KM) kk += st.Fs;
-        if constexpr (CODE == D_TAU_FAT) {
-            ka += st.dA;
-            kt += st.dT1;
-            kk += st.dKm;
-        }
-        k[2] = ka;
-        k[3] = kt;
-        k[4] = kk;
-    }
 }
 
 // ---- one RK stage of one REDUCED tangent column (fatigue models, see dir_reduced) ------------
@@ -778,7 +747,7 @@ FES_HD void rk_step_scheme(const Traj<T> &tr, const Interval<T, Dirs<KIND, FAT, 
             if constexpr (dir_reduced(FAT, C))
                 column_rhs_red<T, KIND, C, s == 0, CNF>(tr, st, eps, iv.sE[d], iv.dg[d], pc_dl, pc_psi, mu_s, nu_s, M_s, R_s, vs[d], k);
             else
-                column_rhs<T, KIND, FAT, C, s == 0, CNF>(tr, st, eps, iv.sE[d], iv.dg[d], pc_dl, pc_psi, vs[d], k);
+                column_rhs<T, KIND, C, s == 0, CNF>(tr, st, eps, iv.sE[d], iv.dg[d], pc_dl, pc_psi, vs[d], k);
             static_for<0, NX>([&](auto ij) {
                 constexpr int j = decltype(ij)::value;
                 if constexpr (dir_stores(FAT, C, j, CNF)) {
@@ -1043,23 +1012,11 @@ FES_HD void rk_step_scheme(const Traj<T> &tr, const Interval<T, Dirs<KIND, FAT, 
         }
         return;
     }
-#ifdef FES_NOMINAL_AHEAD
-    // experiment: issue the nominal chain of stage s+1 (which depends only on the nominal stage s) ahead of the
-    // columns of stage s, so that its reciprocal chain overlaps their FMAs; two Stage records are live
-    Stage<T> stq[2];
-    nominal_stage(std::integral_constant<int, 0>{}, stq[0]);
-    static_for<0, NS>([&](auto is) {
-        constexpr int s = decltype(is)::value;
-        if constexpr (s + 1 < NS) nominal_stage(std::integral_constant<int, s + 1>{}, stq[(s + 1) & 1]);
-        column_stage(is, stq[s & 1]);
-    });
-#else
     static_for<0, NS>([&](auto is) {
         Stage<T> st;
         nominal_stage(is, st);
         column_stage(is, st);
     });
-#endif
     x[0] = xfma(x[0], dl[NS], iv.E * ps[3]);
 #pragma unroll
     for (int j = 1; j < NXN; ++j) x[j] = xn[j];

@@ -116,7 +116,7 @@ def record(name, kernel, units, ms, out_bytes, in_bytes, dtype, counts, peaks, h
 
 
 def run_configs(wanted, dev, dtype="f64", steps=3, warmup=3, scale=1.0, flush=None, t2=300):
-    """Runs the configurations in `wanted` (strings: "1", "2fwd", "2x0", "2pf", "3", "4", "4b", "4c", "5", "5pf") on `dev`; returns
+    """Runs the configurations in `wanted` (strings: "0", "1", "2fwd", "2x0", "2pf", "3", "4", "4b", "4c", "5", "5pf") on `dev`; returns
     (records, meta)."""
     dt_t = torch.float64 if dtype == "f64" else torch.float32
     esz = 8 if dtype == "f64" else 4
@@ -132,6 +132,32 @@ def run_configs(wanted, dev, dtype="f64", steps=3, warmup=3, scale=1.0, flush=No
     S = 10
     recs = []
     add = lambda *a: recs.append(record(*a[:7], counts, peaks, hbm_peak, a[7]))
+
+    if "0" in wanted:
+        # BASELINE configs[0]: the README example itself -- ONE trajectory through the reference-named class, wall clock of
+        # construction and of integrate() (pageable host arrays in, dict of numpy arrays out), as a user would time it.  The
+        # reference's own figures for this call: 0.105 - 0.19 s per integrate(), 2.9 - 10.8 s per construction.
+        import time as _time
+
+        import cocofest_b200 as cf
+
+        def once():
+            model = cf.DingModelFrequencyWithFatigue(stim_time=[k / 10 for k in range(10)], sum_stim_truncation=20)
+            t0 = _time.perf_counter()
+            ivp = cf.IvpFes({"model": model}, {"final_time": 1, "ode_solver": cf.OdeSolver.RK4(n_integration_steps=10)}, device=dev)
+            t1 = _time.perf_counter()
+            res, _ = ivp.integrate()
+            return t1 - t0, _time.perf_counter() - t1, float(res["F"][0, -1])
+
+        for _ in range(3):
+            once()
+        runs = [once() for _ in range(20)]
+        build_ms = 1e3 * statistics.median(r[0] for r in runs)
+        integ_ms = 1e3 * statistics.median(r[1] for r in runs)
+        recs.append({"config": "0: README IvpFes example, ONE trajectory (n_stim = 10, final_time = 1 s, 100 RK4 steps), wall clock per call",
+                     "value": 1e3 / integ_ms, "unit": "integrate() calls/s", "ms": integ_ms, "construction_ms": build_ms, "dtype": "f64",
+                     "F_end": runs[0][2], "roofline": None, "hbm": {"frac": None},
+                     "reference": "0.105 - 0.19 s per integrate(), 2.9 - 10.8 s per IvpFes(...) construction (BASELINE.md section 1)"})
 
     if "1" in wanted:
         # README IVP: DingModelFrequencyWithFatigue, stim 0..0.9 s at 10 Hz, N = 20, T = 1 -> ns = 10, all 101 points
@@ -250,7 +276,7 @@ def run_configs(wanted, dev, dtype="f64", steps=3, warmup=3, scale=1.0, flush=No
 
 def main():
     ap = argparse.ArgumentParser()
-    ap.add_argument("--configs", default="1,3,4,4b,4c,5")
+    ap.add_argument("--configs", default="0,1,3,4,4b,4c,5")
     ap.add_argument("--scale", type=float, default=1.0)
     ap.add_argument("--t2", type=int, default=300, help="protocol length of config 2 in seconds")
     ap.add_argument("--steps", type=int, default=3)

@@ -1,7 +1,7 @@
 #!/usr/bin/env python
 """Writes the DRAM traffic of one `ncu --set full` capture of the bench kernel to profiles/r02_ivp_x0_traffic.json together
-with the sha256 of the library it was captured from (cocofest_b200/csrc/sass_counts.json); bench.py reports it as
-`roofline.traffic` only while the loaded library has that sha256.
+with the sha256 of the device code (SASS dump) of the library it was captured from (cocofest_b200/csrc/sass_counts.json);
+bench.py reports it as `roofline.traffic` only while the loaded library holds that device code.
 Usage: ncu_traffic.py report.ncu-rep summary.tsv [batch] [final_time_s] [dtype]"""
 import csv
 import io
@@ -33,9 +33,9 @@ def get(name, scale=None):
 
 
 rd, wr = get("dram__bytes_read.sum", "bytes"), get("dram__bytes_write.sum", "bytes")
-sha = json.loads((ROOT / "cocofest_b200" / "csrc" / "sass_counts.json").read_text())["lib_sha256"]
+sha = json.loads((ROOT / "cocofest_b200" / "csrc" / "sass_counts.json").read_text())["sass_sha256"]
 d = {
-    "report": f"{rep} (summary: {summary})", "batch": batch, "final_time_s": final_time, "dtype": dtype, "lib_sha256": sha,
+    "report": f"{rep} (summary: {summary})", "batch": batch, "final_time_s": final_time, "dtype": dtype, "sass_sha256": sha,
     "dram_bytes_read": int(rd), "dram_bytes_write": int(wr), "dram_bytes": int(rd + wr),
     "gpu_time_duration_s": get("gpu__time_duration.sum", "seconds"),
     "fp64_pipe_active_pct": get("sm__pipe_fp64_cycles_active.avg.pct_of_peak_sustained_active"),

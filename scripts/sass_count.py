@@ -4,7 +4,8 @@
     python scripts/sass_count.py [--lib cocofest_b200/csrc/libfes_b200.so] [--out cocofest_b200/csrc/sass_counts.json]
 
 Run by cocofest_b200/csrc/Makefile right after the link, so the counts always describe the .so next to them; bench.py
-recomputes the library's sha256 and refuses the counts when it differs.  For every kernel: the RK4 path is the largest
+recomputes the library's sha256 and refuses the counts when it differs (`sass_sha256`, the hash of the device code alone, is
+what survives a re-link of the same sources and ties ncu captures to a build).  For every kernel: the RK4 path is the largest
 straight-line segment (between branches) of the function by floating-point instruction count -- one uniform branch
 per step selects the scheme (fes_core.cuh rk_step), so the whole RK4 step of a trajectory is ONE basic block -- and the
 record holds its instruction mix (DFMA/DMUL/DADD, FFMA/FMUL/FADD and their packed f32x2 forms, MUFU), the function's
@@ -52,6 +53,9 @@ def main():
     lib = Path(args.lib)
     sha = hashlib.sha256(lib.read_bytes()).hexdigest()
     sass = subprocess.run(["cuobjdump", "-sass", str(lib)], capture_output=True, text=True, check=True).stdout
+    # the file hash changes with every link (build id); the device code does not: two builds of the same sources give the
+    # same SASS dump, which is what measurements taken with one build (ncu traffic) are tied to
+    sass_sha = hashlib.sha256(sass.encode()).hexdigest()
     res = subprocess.run(["cuobjdump", "-res-usage", str(lib)], capture_output=True, text=True, check=True).stdout
     usage = {}
     for m in re.finditer(r"Function (\S+):\s*\n\s*REG:(\d+) STACK:(\d+) SHARED:(\d+) LOCAL:(\d+)", res):
@@ -94,7 +98,7 @@ def main():
         }
         rec.update(usage.get(sym, {}))
         kernels[pretty(sym)] = rec
-    out = {"lib": lib.name, "lib_sha256": sha, "how": "scripts/sass_count.py: largest straight-line segment by fp instructions "
+    out = {"lib": lib.name, "lib_sha256": sha, "sass_sha256": sass_sha, "how": "scripts/sass_count.py: largest straight-line segment by fp instructions "
            "= the RK4 step of one trajectory (all tangent columns included)", "kernels": kernels}
     Path(args.out).write_text(json.dumps(out, indent=1, sort_keys=True) + "\n")
     print(f"{len(kernels)} kernels, lib sha256 {sha[:16]}.. -> {args.out}")
