@@ -282,39 +282,15 @@ class ShootResult:
     p_columns: tuple
 
 
-def shoot(kind, fatigue, params, X, win, dt, n_steps=10, ctrl=None, scheme=4, want=("x",), t_start=0.0, tauc=None,
-          r0_km=R0_KM_RELATIONSHIP, defects=True, endpoints=False, dtype=None) -> ShootResult:
-    """All intervals of all scenarios at once.
-
-    X [ns+1, nx, B];  params [14] | [14,B];  win [>=ns,N] | [>=ns,N,B];  ctrl None | [ns,nu] | [ns,nu,B].
-    want: subset of {"x", "u", "p", "pf", "w"} selecting the Jacobian blocks.
-    """
-    X = torch.as_tensor(X)
-    device, dtype, B, N, flags, params, win, ctrl = _common(kind, fatigue, params, win, ctrl, X, dtype)
-    nx, nu = _nx(fatigue), _nu(kind, N)
-    X = _prep(X, dtype, device)
-    ns = X.shape[0] - 1
-    if X.dim() != 3 or X.shape[1] != nx or ns < 1:
-        raise ValueError(f"X must be [ns+1, {nx}, B]")
-    if win.shape[0] < ns or (ctrl is not None and ctrl.shape[0] < ns):
-        raise ValueError("stim window / controls have fewer rows than n_shooting")
-    want = set(want)
-    if not want <= {"x", "u", "p", "pf", "w"}:
-        raise ValueError("want must be a subset of {'x','u','p','pf','w'}")
-    if "pf" in want:
-        if not fatigue:
-            raise ValueError("'pf' (fatigue parameters) needs a fatigue model")
-        want.add("p")
-    if nu == 0:
-        want.discard("u")
+def _shoot_layout(kind, fatigue, nx, nu, N, want):
+    """Column counts of the Jacobian blocks (x, u, p, w), the names of the p columns and the kernel passes
+    [(dirs, tile_offset, first column)] that fill them."""
     tiles = lambda n: (n + FES_TILE - 1) // FES_TILE
     cx = nx if "x" in want else 0
     cu = (1 if kind == FES_DING2007 else tiles(nu) * FES_TILE) if "u" in want else 0
     np_cols = P_COLUMNS[kind] + (PF_COLUMNS if "pf" in want else ()) if "p" in want else ()
     cp = len(np_cols)
     cw = tiles(N) * FES_TILE if "w" in want else 0
-    cols = cx + cu + cp + cw
-    # passes: (dirs, tile_offset, first column)
     passes = []
     if cx and cu:
         passes.append((FES_DIR_X0 | FES_DIR_U, 0, 0))
@@ -331,6 +307,41 @@ def shoot(kind, fatigue, params, X, win, dt, n_steps=10, ctrl=None, scheme=4, wa
         passes.append((FES_DIR_W, t * FES_TILE, cx + cu + cp + t * FES_TILE))
     if not passes:
         passes.append((0, 0, 0))
+    return cx, cu, cp, cw, tuple(np_cols), passes
+
+
+def _normalise_want(kind, fatigue, nu, want):
+    want = set(want)
+    if not want <= {"x", "u", "p", "pf", "w"}:
+        raise ValueError("want must be a subset of {'x','u','p','pf','w'}")
+    if "pf" in want:
+        if not fatigue:
+            raise ValueError("'pf' (fatigue parameters) needs a fatigue model")
+        want.add("p")
+    if nu == 0:
+        want.discard("u")
+    return want
+
+
+def shoot(kind, fatigue, params, X, win, dt, n_steps=10, ctrl=None, scheme=4, want=("x",), t_start=0.0, tauc=None,
+          r0_km=R0_KM_RELATIONSHIP, defects=True, endpoints=False, dtype=None) -> ShootResult:
+    """All intervals of all scenarios at once.
+
+    X [ns+1, nx, B];  params [14] | [14,B];  win [>=ns,N] | [>=ns,N,B];  ctrl None | [ns,nu] | [ns,nu,B].
+    want: subset of {"x", "u", "p", "pf", "w"} selecting the Jacobian blocks.
+    """
+    X = torch.as_tensor(X)
+    device, dtype, B, N, flags, params, win, ctrl = _common(kind, fatigue, params, win, ctrl, X, dtype)
+    nx, nu = _nx(fatigue), _nu(kind, N)
+    X = _prep(X, dtype, device)
+    ns = X.shape[0] - 1
+    if X.dim() != 3 or X.shape[1] != nx or ns < 1:
+        raise ValueError(f"X must be [ns+1, {nx}, B]")
+    if win.shape[0] < ns or (ctrl is not None and ctrl.shape[0] < ns):
+        raise ValueError("stim window / controls have fewer rows than n_shooting")
+    want = _normalise_want(kind, fatigue, nu, want)
+    cx, cu, cp, cw, np_cols, passes = _shoot_layout(kind, fatigue, nx, nu, N, want)
+    cols = cx + cu + cp + cw
 
     L = _lib.lib()
     is32 = dtype == torch.float32
@@ -391,6 +402,104 @@ def shoot(kind, fatigue, params, X, win, dt, n_steps=10, ctrl=None, scheme=4, wa
     o += cp
     Jw = J[:, :, o:o + N] if cw else None
     return ShootResult(G, Phi, Jx, Ju, Jp, Jw, tuple(np_cols))
+
+
+class ShootPlan:
+    """One multiple-shooting evaluation (defects + the requested Jacobian blocks of B scenarios x ns intervals) set up
+    ONCE and called once per solver iteration -- what a built OCP is to the reference (``prepare_ocp`` builds the casadi
+    graph once, Ipopt evaluates it per iteration).  Everything that does not change between iterations is done at
+    construction: argument checks, the pass list, the output tensors, the workspaces and -- on the first call -- the
+    window tables, which later calls reuse (``FES_TABLES_READY``).  A call then only hands the library the pointers of
+    the current node states / controls / parameters and launches the passes: ~10 us of host work instead of the ~50 us
+    of a one-shot ``shoot()``, which for config 5 (0.46 ms of kernel time) is 10 % of the call.
+
+    The results are written into the plan's OWN tensors on every call (views of them are returned): copy what must
+    survive the next call.  Device tensors only; inputs must have the dtype and shapes given at construction; the window
+    tables are built on the stream of the first call, so keep the calls of one plan on one stream (or synchronise once).
+    """
+
+    def __init__(self, kind, fatigue, params, win, dt, n_shooting, batch, n_steps=10, ctrl=None, scheme=4, want=("x",),
+                 t_start=0.0, tauc=None, r0_km=R0_KM_RELATIONSHIP, defects=True, endpoints=False, dtype=torch.float64):
+        win = torch.as_tensor(win)
+        device = win.device
+        if device.type != "cuda" and not _lib.is_host_emulation():   # (the test suite's host build takes host pointers)
+            raise ValueError("ShootPlan works on CUDA tensors (use shoot() for host tensors)")
+        lead = torch.empty((1, int(batch)), dtype=dtype, device=device)
+        _, _, B, N, flags, params, win, ctrl = _common(kind, fatigue, params, win, ctrl, lead, dtype)
+        self.kind, self.fatigue, self.dtype, self.device = kind, bool(fatigue), dtype, device
+        self.B, self.N, self.ns, self.nx, self.nu = B, N, int(n_shooting), _nx(fatigue), _nu(kind, N)
+        if win.shape[0] < self.ns:
+            raise ValueError("stim window has fewer rows than n_shooting")
+        if self.nu and ctrl is None:
+            raise ValueError("this model needs controls: pass a template `ctrl` of the shape later calls will use")
+        self._params, self._win, self._ctrl = params, win, ctrl
+        want = _normalise_want(kind, fatigue, self.nu, want)
+        cx, cu, cp, cw, self.p_columns, passes = _shoot_layout(kind, fatigue, self.nx, self.nu, N, want)
+        self._cols = (cx, cu, cp, cw)
+        cols = cx + cu + cp + cw
+        ns, nx = self.ns, self.nx
+        self.G = torch.empty((ns, nx, B), dtype=dtype, device=device) if defects else None
+        self.Phi = torch.empty((ns, nx, B), dtype=dtype, device=device) if endpoints else None
+        self.J = torch.empty((ns, nx, cols, B), dtype=dtype, device=device) if cols else None
+        L = _lib.lib()
+        self._is32 = dtype == torch.float32
+        self._fn = L.fes_shoot_f32 if self._is32 else L.fes_shoot_f64
+        self._passes, self._ws = [], {}
+        first = True
+        with self._on_device():
+            for dirs, tile_off, col0 in passes:
+                desc = _desc(kind, fatigue, scheme, N, ns, n_steps, dirs, flags, B, dt, t_start, tauc, r0_km, tile_offset=tile_off)
+                slot = kind == FES_HMED2018 or bool(dirs & FES_DIR_W)   # table layout: per-slot weights or sums only
+                wbytes = L.fes_workspace_bytes(ctypes.byref(desc), int(self._is32))
+                if slot not in self._ws:
+                    self._ws[slot] = [torch.empty(max(int(wbytes), 1), dtype=torch.uint8, device=device), False]
+                buf = FesShootBuffers(_ptr(params), None, _ptr(win), _ptr(ctrl), _ptr(self.G) if first else None,
+                                      _ptr(self.Phi) if first else None, _ptr(self.J), cols, col0,
+                                      self._ws[slot][0].data_ptr(), wbytes)
+                self._passes.append((desc, buf, slot))
+                first = False
+
+    def _on_device(self):
+        import contextlib
+
+        return torch.cuda.device(self.device) if self.device.type == "cuda" else contextlib.nullcontext()
+
+    def __call__(self, X, ctrl=None, params=None) -> "ShootResult":
+        """X [ns+1, nx, B];  ctrl [ns, nu(, B)] when the model has controls (default: the tensor given at construction);
+        params [14(, B)] (default: the tensor given at construction)."""
+        ns, nx, B = self.ns, self.nx, self.B
+
+        def check(t, like, name):
+            if t is None:
+                return like
+            if t.dtype != like.dtype or t.device != like.device or tuple(t.shape) != tuple(like.shape) or not t.is_contiguous():
+                raise ValueError(f"{name}: expected a contiguous {like.dtype} tensor of shape {tuple(like.shape)} on {like.device}")
+            return t
+
+        if X.dtype != self.dtype or X.device != self.device or tuple(X.shape) != (ns + 1, nx, B) or not X.is_contiguous():
+            raise ValueError(f"X: expected a contiguous {self.dtype} tensor of shape {(ns + 1, nx, B)} on {self.device}")
+        ctrl = check(ctrl, self._ctrl, "ctrl") if self.nu else None
+        params = check(params, self._params, "params")
+        stream = ctypes.c_void_p(_stream_ptr(self.device))
+        with self._on_device():
+            for desc, buf, slot in self._passes:
+                buf.X, buf.params = X.data_ptr(), params.data_ptr()
+                buf.ctrl = None if ctrl is None else ctrl.data_ptr()
+                state = self._ws[slot]
+                if state[1]:
+                    desc.flags |= _lib.FES_TABLES_READY
+                _lib.check(self._fn(ctypes.byref(desc), ctypes.byref(buf), stream), "fes_shoot")
+                state[1] = True
+        cx, cu, cp, cw = self._cols
+        J, o = self.J, 0
+        Jx = J[:, :, o:o + cx] if cx else None
+        o += cx
+        Ju = J[:, :, o:o + self.nu] if cu else None
+        o += cu
+        Jp = J[:, :, o:o + cp] if cp else None
+        o += cp
+        Jw = J[:, :, o:o + self.N] if cw else None
+        return ShootResult(self.G, self.Phi, Jx, Ju, Jp, Jw, self.p_columns)
 
 
 @dataclass

@@ -68,6 +68,16 @@ class FesShooting:
                           want=want, t_start=self.t_start, tauc=self.model.tauc, r0_km=self.model.r0_km_relationship,
                           defects=defects, endpoints=endpoints, dtype=self.dtype)
 
+    def plan(self, batch, U=None, params=None, want=("x", "u"), defects=True, endpoints=False) -> _fes.ShootPlan:
+        """The same evaluation set up once for a solver loop (``fes.ShootPlan``): ``p = shooting.plan(B, U0); res = p(X, U)``
+        per iteration.  ``U`` / ``params`` are templates of the shapes the calls will use; the plan's result tensors are
+        reused from call to call."""
+        return _fes.ShootPlan(self.model.kind, self.model.with_fatigue, self._params(params), self.window, self.dt,
+                              self.n_shooting, batch, n_steps=self.n_steps,
+                              ctrl=None if U is None else torch.as_tensor(U).to(self.device), scheme=self.scheme, want=want,
+                              t_start=self.t_start, tauc=self.model.tauc, r0_km=self.model.r0_km_relationship,
+                              defects=defects, endpoints=endpoints, dtype=self.dtype)
+
     def defects(self, X, U=None, params=None) -> torch.Tensor:
         """g [ns, nx, B]: the continuity constraint values (penalty.py:1092-1099)."""
         return self.evaluate(X, U, params, want=()).G

@@ -256,12 +256,19 @@ def run_configs(wanted, dev, dtype="f64", steps=3, warmup=3, scale=1.0, flush=No
         win = torch.tensor(proto["win"], device=dev)
         ns = proto["ns"]
         if "5" in wanted:
-            fn = lambda: fes.shoot(fes.FES_DING2007, True, p, X, win, proto["dt"], n_steps=S, ctrl=U, want=("x", "u"), dtype=dt_t)
+            # a built problem evaluated once per solver iteration: the plan is what prepare_ocp is to the reference (set-up and
+            # window tables once), the timed call is one Ipopt iteration's worth of defects and Jacobian blocks
+            plan = fes.ShootPlan(fes.FES_DING2007, True, p, win, proto["dt"], ns, B, n_steps=S, ctrl=U, want=("x", "u"), dtype=dt_t)
+            fn = lambda: plan(X, U)
             out, ms = timed(fn, steps, warmup, flush)
             ob = (out.G.numel() + out.Jx.numel() + out.Ju.numel()) * esz
-            add("5: NMPC cyclic horizon, 64K scenarios x 33 intervals, defects + dPhi/dx + dPhi/dpw",
+            one_shot, ms1 = timed(lambda: fes.shoot(fes.FES_DING2007, True, p, X, win, proto["dt"], n_steps=S, ctrl=U, want=("x", "u"),
+                                                    dtype=dt_t), steps, warmup, flush)
+            assert torch.equal(one_shot.Jx, out.Jx) and torch.equal(one_shot.G, out.G)
+            add("5: NMPC cyclic horizon, 64K scenarios x 33 intervals, defects + dPhi/dx + dPhi/dpw (ShootPlan call per iteration)",
                 kernel_name("shoot", dtype, fes.FES_DING2007, True, fes.FES_DIR_X0 | fes.FES_DIR_U), B * ns * S, ms, ob,
-                (X.numel() + U.numel()) * esz, dtype, {"scenarios": B, "n_shooting": ns, "interval_integrations": B * ns})
+                (X.numel() + U.numel()) * esz, dtype, {"scenarios": B, "n_shooting": ns, "interval_integrations": B * ns,
+                                                       "one_shot_shoot_call_ms": statistics.mean(ms1)})
         if "5pf" in wanted:
             # the dense parameter columns of a fatigue model (what a fatigue-parameter identification would differentiate)
             fn = lambda: fes.shoot(fes.FES_DING2007, True, p, X, win, proto["dt"], n_steps=S, ctrl=U, want=("p", "pf"),

@@ -143,3 +143,31 @@ def test_chained_shoot_jacobians_equal_ivp_sensitivities(backend):
     scale = iv.sens_final.abs().amax(dim=2, keepdim=True)   # every (row, column) entry on its own scale
     assert bool((M[scale.expand_as(M) == 0] == 0).all())     # structural zeros (d Cn / d anything but Cn0) stay zero
     assert float(((M - iv.sens_final).abs() / scale.clamp_min(1e-300)).max()) < 1e-9
+
+
+@pytest.mark.parametrize("backend", BACKENDS, indirect=True)
+@pytest.mark.parametrize("name", ["ding2003_with_fatigue", "ding2007_with_fatigue", "hmed2018"])
+def test_shoot_plan_equals_one_shot_calls_and_reuses_its_tables(backend, name):
+    """ShootPlan = shoot() with the set-up done once: same bits on every call, for new node states / controls / parameters."""
+    from cocofest_b200 import _lib
+
+    pb = random_problem(name, B=9, N=7, ns=8, seed=21, shared_ctrl=False)
+    params, _, win, ctrl = to_lib(pb, backend)
+    want = ("x", "u", "p", "w")
+    plan = fes.ShootPlan(pb["kind"], pb["fat"], params, win, pb["dt"], pb["ns"], pb["B"], n_steps=4, ctrl=ctrl, want=want,
+                         endpoints=True)
+    n0 = _lib.lib().fes_launch_count()
+    for it in range(3):
+        X = torch.tensor(np.ascontiguousarray(np.transpose(_X(pb, seed=it), (1, 2, 0))), device=backend)
+        u_it = None if ctrl is None else (ctrl * (1.0 + 0.01 * it)).contiguous()
+        p_it = (params * (1.0 + 0.001 * it)).contiguous()
+        got = plan(X, ctrl=u_it, params=p_it)
+        ref = fes.shoot(pb["kind"], pb["fat"], p_it, X, win, pb["dt"], n_steps=4, ctrl=u_it, want=want, endpoints=True)
+        for a, b in ((got.G, ref.G), (got.Phi, ref.Phi), (got.Jx, ref.Jx), (got.Ju, ref.Ju), (got.Jp, ref.Jp), (got.Jw, ref.Jw)):
+            assert (a is None and b is None) or torch.equal(a, b)
+        assert got.p_columns == ref.p_columns
+    if backend.type == "cuda":   # the plan builds each table layout once; the one-shot call rebuilds it per layout change
+        per_plan_call = len(plan._passes)
+        assert _lib.lib().fes_launch_count() - n0 >= 3 * per_plan_call
+    with pytest.raises(ValueError, match="X: expected"):
+        plan(X[:-1].contiguous())
