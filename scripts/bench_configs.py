@@ -274,7 +274,7 @@ def run_configs(wanted, dev, dtype="f64", steps=3, warmup=3, scale=1.0, flush=No
             fn = lambda: fes.shoot(fes.FES_DING2007, True, p, X, win, proto["dt"], n_steps=S, ctrl=U, want=("p", "pf"),
                                    defects=False, dtype=dt_t)
             out, ms = timed(fn, steps, warmup, flush)
-            add("5pf: the same horizon, dPhi/d(6 model + 4 fatigue parameters): dense 5-component columns",
+            add("5pf: the same horizon, dPhi/d(6 model + 4 fatigue parameters): reduced parameter columns through the 2 x 2 step propagator",
                 kernel_name("shoot", dtype, fes.FES_DING2007, True, fes.FES_DIR_P | fes.FES_DIR_PF), B * ns * S, ms,
                 out.Jp.numel() * esz, (X.numel() + U.numel()) * esz, dtype, {"scenarios": B, "n_shooting": ns})
     meta = {"sass_counts": counts_src, "nominal_peaks": peaks}
