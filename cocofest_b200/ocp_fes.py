@@ -78,6 +78,61 @@ class FesShooting:
                               t_start=self.t_start, tauc=self.model.tauc, r0_km=self.model.r0_km_relationship,
                               defects=defects, endpoints=endpoints, dtype=self.dtype)
 
+    # ---- second derivatives (for an exact-Hessian solver) ---------------------------------------------
+    # typical magnitudes of (Cn, F, A, Tau1, Km) and of the controls: floors of the finite-difference steps
+    _STATE_SCALE = (0.1, 10.0, 1000.0, 0.05, 0.1)
+
+    def second_derivatives(self, X, U=None, params=None, rel_step=1e-5):
+        """d2 Phi_k / d z_k d z_k for z_k = (x_k, u_k): tensor [ns, nx, nz, nz, B], nz = nx + nu.
+
+        The reference's Ipopt runs on casadi's exact Hessian by default (bioptim interfaces/ipopt_options.py:88).  The
+        kernels propagate first-order tangents only; this evaluates the second derivatives as CENTRAL DIFFERENCES OF THE
+        EXACT JACOBIAN blocks -- 2 nz evaluations of one ``ShootPlan`` (every interval of every scenario is perturbed in the
+        same call: interval k depends on x_k, u_k only) -- and symmetrises.  With the Jacobian exact to rounding the error
+        is O(rel_step^2) truncation + O(1e-16 / rel_step) rounding: ~1e-10 relative at the default step (measured against
+        complex-step differentiation of the oracle, tests/test_second_derivatives.py).  Not a second-order tangent
+        propagation; DESIGN.md section 8 lists that as open."""
+        X = torch.as_tensor(X).to(self.device).contiguous()
+        ns, nx, nu = self.n_shooting, self.nx, self.nu
+        B = X.shape[-1]
+        if nu:
+            U = torch.as_tensor(U).to(self.device)
+            if U.dim() == 2:
+                U = U[:, :, None].expand(ns, nu, B)
+            U = U.contiguous()
+        plan = self.plan(B, U, params, want=("x", "u") if nu else ("x",), defects=False, endpoints=False)
+        nz = nx + nu
+        out = torch.empty((ns, nx, nz, nz, B), dtype=X.dtype, device=self.device)
+        scale = torch.tensor(self._STATE_SCALE[:nx], dtype=X.dtype, device=self.device)
+
+        def jac(Xp, Up):
+            r = plan(Xp, Up)
+            return r.Jx.clone() if not nu else torch.cat([r.Jx, r.Ju], dim=2)      # [ns, nx, nz, B]
+
+        for d in range(nz):
+            if d < nx:
+                h = rel_step * torch.maximum(X[:ns, d].abs(), scale[d].expand_as(X[:ns, d]))   # [ns, B]
+                Xp, Xm = X.clone(), X.clone()
+                Xp[:ns, d] += h
+                Xm[:ns, d] -= h
+                h = (Xp[:ns, d] - Xm[:ns, d]) * 0.5        # the step that was really taken
+                out[:, :, :, d] = (jac(Xp, U) - jac(Xm, U)) / (2.0 * h[:, None, None, :])
+            else:
+                j = d - nx
+                h = rel_step * U[:, j].abs().clamp_min(1e-30)
+                Up, Um = U.clone(), U.clone()
+                Up[:, j] += h
+                Um[:, j] -= h
+                h = (Up[:, j] - Um[:, j]) * 0.5
+                out[:, :, :, d] = (jac(X, Up) - jac(X, Um)) / (2.0 * h[:, None, None, :])
+        return 0.5 * (out + out.transpose(2, 3))
+
+    @staticmethod
+    def lagrangian_hessian(multipliers, second):
+        """sum_j lambda[k, j] d2 Phi_kj / dz dz: [ns, nz, nz, B] from multipliers [ns, nx, B] and ``second_derivatives``.
+        (The continuity rows are g_k = x_{k+1} - Phi_k: their contribution to the Lagrangian Hessian is minus this.)"""
+        return torch.einsum("kjb,kjdeb->kdeb", multipliers, second)
+
     def defects(self, X, U=None, params=None) -> torch.Tensor:
         """g [ns, nx, B]: the continuity constraint values (penalty.py:1092-1099)."""
         return self.evaluate(X, U, params, want=()).G
