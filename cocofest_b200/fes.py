@@ -271,6 +271,85 @@ def ivp(kind, fatigue, params, x0, win, dt, n_steps=10, ctrl=None, n_shooting=No
     return IvpResult(out_x, out_tr, out_sf, out_st, direction_columns(kind, fatigue, dirs, N), ns, n_steps)
 
 
+class IvpPlan:
+    """A batched integration set up ONCE and run many times (a solver loop over parameters, an identification on the host,
+    repeated ``IvpFes.integrate()`` calls): argument checks, output tensors, workspace and -- on the first call -- the
+    window tables are reused; a call only hands over the pointers of the current initial states / parameters / controls.
+    For the millisecond-sized configurations the ~50 us of host work of a one-shot ``ivp()`` are 5 % of the call.
+
+    Results are written into the plan's OWN tensors on every call.  CUDA tensors only; inputs must keep the dtype and the
+    shapes given at construction; keep the calls of one plan on one stream (the tables are built on the first call's)."""
+
+    def __init__(self, kind, fatigue, params, x0, win, dt, n_steps=10, ctrl=None, n_shooting=None, scheme=4, dirs=0,
+                 t_start=0.0, tauc=None, r0_km=R0_KM_RELATIONSHIP, trace="none", trace_batch=None, sens_trace=False,
+                 dtype=None):
+        x0 = torch.as_tensor(x0)
+        device, dtype, B, N, flags, params, win, ctrl = _common(kind, fatigue, params, win, ctrl, x0, dtype)
+        if device.type != "cuda" and not _lib.is_host_emulation():
+            raise ValueError("IvpPlan works on CUDA tensors (use ivp() for host tensors)")
+        nx = _nx(fatigue)
+        x0 = _prep(x0, dtype, device)
+        if x0.shape != (nx, B):
+            raise ValueError(f"x0 must be [{nx}, B]")
+        ns = n_shooting if n_shooting is not None else (ctrl.shape[0] if ctrl is not None else win.shape[0] - 1)
+        if win.shape[0] < ns or (ctrl is not None and ctrl.shape[0] < ns):
+            raise ValueError("stim window / controls have fewer rows than n_shooting")
+        L = _lib.lib()
+        nd = L.fes_num_dirs(kind, int(bool(fatigue)), dirs)
+        if nd < 0 or dirs & (FES_DIR_U | FES_DIR_W):
+            raise ValueError("ivp supports dirs in {0, X0, P, P|PF}")
+        modes = {"none": 0, "nodes": n_steps, "steps": 1}
+        if trace not in modes:
+            raise ValueError("trace must be 'none', 'nodes' or 'steps'")
+        want_trace = trace != "none" or sens_trace
+        trace_every = modes[trace] if trace != "none" else (n_steps if sens_trace else 0)
+        tB = (B if trace_batch is None else min(int(trace_batch), B)) if want_trace else 0
+        npts = ns * n_steps + 1 if trace_every == 1 else ns + 1
+        self.device, self.dtype, self._x0, self._params, self._ctrl, self._win = device, dtype, x0, params, ctrl, win
+        self._desc = _desc(kind, fatigue, scheme, N, ns, n_steps, dirs, flags, B, dt, t_start, tauc, r0_km,
+                           trace_every=trace_every, trace_batch=tB)
+        new = lambda shape: torch.empty(shape, dtype=dtype, device=device)
+        out_x = new((nx, B))
+        out_tr = new((npts, nx, tB)) if (trace != "none" and tB) else None
+        out_sf = new((nx, nd, B)) if nd else None
+        out_st = new((ns + 1, nx, nd, tB)) if (nd and sens_trace and tB) else None
+        self.result = IvpResult(out_x, out_tr, out_sf, out_st, direction_columns(kind, fatigue, dirs, N), ns, n_steps)
+        self._is32 = dtype == torch.float32
+        self._fn = L.fes_ivp_f32 if self._is32 else L.fes_ivp_f64
+        with self._on_device():
+            wbytes = L.fes_workspace_bytes(ctypes.byref(self._desc), int(self._is32))
+            self._ws = torch.empty(max(int(wbytes), 1), dtype=torch.uint8, device=device)
+        self._buf = FesIvpBuffers(_ptr(params), _ptr(x0), _ptr(win), _ptr(ctrl), _ptr(out_x), _ptr(out_tr), _ptr(out_sf),
+                                  _ptr(out_st), self._ws.data_ptr(), wbytes)
+        self._tables = False
+
+    def _on_device(self):
+        import contextlib
+
+        return torch.cuda.device(self.device) if self.device.type == "cuda" else contextlib.nullcontext()
+
+    def __call__(self, x0=None, params=None, ctrl=None) -> "IvpResult":
+        """x0 [nx, B], params [14(, B)], ctrl [ns, nu(, B)]: default = the tensors given at construction."""
+        def check(t, like, name):
+            if t is None:
+                return like
+            if t.dtype != like.dtype or t.device != like.device or tuple(t.shape) != tuple(like.shape) or not t.is_contiguous():
+                raise ValueError(f"{name}: expected a contiguous {like.dtype} tensor of shape {tuple(like.shape)} on {like.device}")
+            return t
+
+        x0, params = check(x0, self._x0, "x0"), check(params, self._params, "params")
+        buf = self._buf
+        buf.x0, buf.params = x0.data_ptr(), params.data_ptr()
+        if self._ctrl is not None:
+            buf.ctrl = check(ctrl, self._ctrl, "ctrl").data_ptr()
+        if self._tables:
+            self._desc.flags |= _lib.FES_TABLES_READY
+        with self._on_device():
+            _lib.check(self._fn(ctypes.byref(self._desc), ctypes.byref(buf), ctypes.c_void_p(_stream_ptr(self.device))), "fes_ivp")
+        self._tables = True
+        return self.result
+
+
 @dataclass
 class ShootResult:
     G: torch.Tensor | None      # [ns, nx, B]   g_k = x_{k+1} - Phi_k

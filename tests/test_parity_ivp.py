@@ -295,3 +295,23 @@ def test_ivp_out_buffers_are_reused(backend):
     assert all(torch.equal(g, r) for g, r in zip(got, ref))
     with pytest.raises(ValueError, match="out: expected"):
         fes.ivp(pb["kind"], pb["fat"], params, x0, win, pb["dt"], out=a, **{**kw, "n_shooting": pb["ns"] - 1})
+
+
+@pytest.mark.parametrize("backend", BACKENDS, indirect=True)
+@pytest.mark.parametrize("name", ["ding2003_with_fatigue", "ding2007", "hmed2018_with_fatigue"])
+def test_ivp_plan_equals_one_shot_calls(backend, name):
+    """IvpPlan = ivp() with the set-up done once: same bits on every call, for new initial states / parameters / controls."""
+    pb = random_problem(name, B=11, seed=6, shared_ctrl=False)
+    params, x0, win, ctrl = to_lib(pb, backend)
+    kw = dict(n_steps=5, n_shooting=pb["ns"], dirs=fes.FES_DIR_X0, trace="nodes", sens_trace=True, trace_batch=4)
+    plan = fes.IvpPlan(pb["kind"], pb["fat"], params, x0, win, pb["dt"], ctrl=ctrl, **kw)
+    for it in range(3):
+        x_it, p_it = (x0 * (1.0 + 0.01 * it)).contiguous(), (params * (1.0 + 0.002 * it)).contiguous()
+        u_it = None if ctrl is None else (ctrl * (1.0 - 0.01 * it)).contiguous()
+        got = plan(x_it, p_it, u_it)
+        ref = fes.ivp(pb["kind"], pb["fat"], p_it, x_it, win, pb["dt"], ctrl=u_it, **kw)
+        for a, b in ((got.x_final, ref.x_final), (got.trace, ref.trace), (got.sens_final, ref.sens_final), (got.sens_trace, ref.sens_trace)):
+            assert torch.equal(a, b)
+        assert got.columns == ref.columns
+    with pytest.raises(ValueError, match="x0: expected"):
+        plan(x0[:, :-1].contiguous())
