@@ -1043,6 +1043,19 @@ FES_HD void rk_step_scheme(const Traj<T> &tr, const Interval<T, Dirs<KIND, FAT, 
     }
 }
 
+// U consecutive RK4 steps (i0 .. i0 + U - 1 of the interval) as ONE basic block: no scheme branch and no loop back edge between
+// them, so that the instruction scheduler can start the nominal stage chain of step i + 1 (a serial chain: reciprocal -> q -> F'
+// -> next stage state) while the propagator / column phase of step i is still in flight.  tbl = the stage table of the call.
+template <typename T, int KIND, bool FAT, int GROUPS, int U>
+FES_HD void rk4_steps(const Traj<T> &tr, const Interval<T, Dirs<KIND, FAT, GROUPS>::ND> &iv, T h, const T *tbl, int S, int i0,
+                      T *x, Tangent<T, KIND, FAT, GROUPS> &tg) {
+    static_for<0, U>([&](auto iu) {
+        const int i = i0 + decltype(iu)::value;
+        const T e[3] = {tbl[2 * i], tbl[2 * i + 1], tbl[2 * i + 2]};
+        rk_step_scheme<T, KIND, FAT, GROUPS, 4>(tr, iv, h, e, tbl + 2 * S + 1 + 4 * i, x, tg);
+    });
+}
+
 // e0, e1, e2 = eps at the step start, midpoint and end.  ONE uniform branch per step selects the scheme.
 template <typename T, int KIND, bool FAT, int GROUPS>
 FES_HD void rk_step(const Traj<T> &tr, const Interval<T, Dirs<KIND, FAT, GROUPS>::ND> &iv, int scheme, T h,

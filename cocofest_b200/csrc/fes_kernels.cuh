@@ -30,6 +30,11 @@ namespace fes {
 #define FES_BLOCK 64
 #endif
 constexpr int BLOCK = FES_BLOCK;
+// RK4 steps fused into one basic block (rk4_steps in fes_core.cuh); measured on the B200, see DESIGN.md section 4
+#ifndef FES_STEP_UNROLL
+#define FES_STEP_UNROLL 1
+#endif
+constexpr int STEP_UNROLL = FES_STEP_UNROLL;
 // Resident blocks per SM the compiler must make room for.  The fp64 fatigue kernels whose columns are all
 // "reduced" (fes_core.cuh) take ~188 registers when unconstrained.  Asking for 5 blocks of 64 threads (a cap of
 // 204 registers) makes ptxas settle on 162 registers = 6 resident blocks = 12 warps/SM with a schedule that
@@ -196,7 +201,11 @@ __global__ void FES_LAUNCH_BOUNDS fes_ivp_kernel(const IvpArgs<T> a) {
             Interval<T, ND> iv;
             interval_setup<T, KIND, FAT, GROUPS>(
                 tr, [&](int c) { return trow[c * tstr]; }, [&](int c) { return crow[c * cstr]; }, a.N, a.tile_off, iv, lcp);
-            for (int i = 0; i < a.S; ++i) {
+            int i = 0;
+            if (a.scheme == 4 && !(tr_on && a.trace_mode == 1))
+                for (; i + STEP_UNROLL <= a.S; i += STEP_UNROLL)
+                    rk4_steps<T, KIND, FAT, GROUPS, STEP_UNROLL>(tr, iv, a.h, s_eps, a.S, i, x, tg);
+            for (; i < a.S; ++i) {
                 rk_step<T, KIND, FAT, GROUPS>(tr, iv, a.scheme, a.h, s_eps[2 * i], s_eps[2 * i + 1], s_eps[2 * i + 2],
                                               s_eps + 2 * a.S + 1 + 4 * i, x, tg);
                 if (tr_on && a.trace_mode == 1) put_state((int64_t)node * a.S + i + 1);
@@ -285,7 +294,11 @@ __global__ void FES_LAUNCH_BOUNDS fes_shoot_kernel(const ShootArgs<T> a) {
         interval_setup<T, KIND, FAT, GROUPS>(
             tr, [&](int c) { return __ldg(trow + c * a.tB); }, [&](int c) { return __ldg(crow + c * a.cB); }, a.N,
             a.tile_off, iv);
-    for (int i = 0; i < a.S; ++i)
+    int i = 0;
+    if (a.scheme == 4)
+        for (; i + STEP_UNROLL <= a.S; i += STEP_UNROLL)
+            rk4_steps<T, KIND, FAT, GROUPS, STEP_UNROLL>(tr, iv, a.h, s_eps, a.S, i, x, tg);
+    for (; i < a.S; ++i)
         rk_step<T, KIND, FAT, GROUPS>(tr, iv, a.scheme, a.h, s_eps[2 * i], s_eps[2 * i + 1], s_eps[2 * i + 2],
                                       s_eps + 2 * a.S + 1 + 4 * i, x, tg);
 
