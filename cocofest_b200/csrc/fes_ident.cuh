@@ -115,9 +115,10 @@ FES_HD void ident_eval(const IdentArgs<T> &a, const IdentRows<T, UNIT> &rows, in
                 tr, [&](int c) { return trow[c * rows.t_col]; }, [&](int c) { return crow[c * rows.c_col]; }, a.N, 0, iv, lcp);
         }
         int i = 0;
-        if (a.scheme == 4)
-            for (; i + STEP_UNROLL <= a.S; i += STEP_UNROLL)
-                rk4_steps<T, KIND, false, G_P, STEP_UNROLL>(tr, iv, a.h, eps, a.S, i, x, tg);
+        if constexpr (FES_IDENT_UNROLL > 1)
+            if (a.scheme == 4)
+                for (; i + FES_IDENT_UNROLL <= a.S; i += FES_IDENT_UNROLL)
+                    rk4_steps<T, KIND, false, G_P, FES_IDENT_UNROLL>(tr, iv, a.h, eps, a.S, i, x, tg);
         for (; i < a.S; ++i)
             rk_step<T, KIND, false, G_P>(tr, iv, a.scheme, a.h, eps[2 * i], eps[2 * i + 1], eps[2 * i + 2],
                                          eps + 2 * a.S + 1 + 4 * i, x, tg);

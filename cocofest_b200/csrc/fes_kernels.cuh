@@ -30,11 +30,28 @@ namespace fes {
 #define FES_BLOCK 64
 #endif
 constexpr int BLOCK = FES_BLOCK;
-// RK4 steps fused into one basic block (rk4_steps in fes_core.cuh); measured on the B200, see DESIGN.md section 4
-#ifndef FES_STEP_UNROLL
-#define FES_STEP_UNROLL 1
+// RK4 steps fused into one basic block (rk4_steps in fes_core.cuh): how many, per kernel family, by measurement on the B200
+// (profiles/r02_tune_step_unroll_{r,s}.txt; u2 / u5 / u10 = blocks of 2 / 5 / 10 steps, S = 10):
+//   trajectory kernel  fp64 headline +2.0 % (u2), +1.7 % (u5), +0.8 % (u10); config 3 +2.2 %; dense P|PF columns +4.0 % (u2);
+//                      fp32 headline +7.7 % (u2), config 3 +10.7 % (u2)                                         -> pairs
+//   interval kernel    fp64 config 5 (X0|U): 0.484 (u1), 0.486 (u2), 0.469 (u5), 0.571 ms (u10); config 5pf (dense P|PF): 0.790 (u1),
+//                      0.758 (u2), 0.804 ms (u5); fp32 config 5: 0.341 (u1), 0.342 (u2), 0.352 ms (u5)  -> 5 / pairs / single (fp32)
+//   identification     10.56 (u1), 10.75 (u2), 11.48 (u5), 12.03 ms (u10): it already spills its Lambda cache under the cap -> single
+#ifndef FES_IVP_UNROLL
+#define FES_IVP_UNROLL 2
 #endif
-constexpr int STEP_UNROLL = FES_STEP_UNROLL;
+#ifndef FES_IDENT_UNROLL
+#define FES_IDENT_UNROLL 1
+#endif
+template <typename T, bool FAT, int GROUPS>
+constexpr int shoot_unroll() {
+#ifdef FES_SHOOT_UNROLL
+    return FES_SHOOT_UNROLL;
+#else
+    if (sizeof(T) == 4) return 1;
+    return (FAT && (GROUPS & (G_P | G_PF))) ? 2 : 5;
+#endif
+}
 // Resident blocks per SM the compiler must make room for.  The fp64 fatigue kernels whose columns are all
 // "reduced" (fes_core.cuh) take ~188 registers when unconstrained.  Asking for 5 blocks of 64 threads (a cap of
 // 204 registers) makes ptxas settle on 162 registers = 6 resident blocks = 12 warps/SM with a schedule that
@@ -201,10 +218,11 @@ __global__ void FES_LAUNCH_BOUNDS fes_ivp_kernel(const IvpArgs<T> a) {
             Interval<T, ND> iv;
             interval_setup<T, KIND, FAT, GROUPS>(
                 tr, [&](int c) { return trow[c * tstr]; }, [&](int c) { return crow[c * cstr]; }, a.N, a.tile_off, iv, lcp);
+            constexpr int UNROLL = FES_IVP_UNROLL;
             int i = 0;
-            if (a.scheme == 4 && !(tr_on && a.trace_mode == 1))
-                for (; i + STEP_UNROLL <= a.S; i += STEP_UNROLL)
-                    rk4_steps<T, KIND, FAT, GROUPS, STEP_UNROLL>(tr, iv, a.h, s_eps, a.S, i, x, tg);
+            if constexpr (UNROLL > 1)
+                if (a.scheme == 4 && !(tr_on && a.trace_mode == 1))
+                    for (; i + UNROLL <= a.S; i += UNROLL) rk4_steps<T, KIND, FAT, GROUPS, UNROLL>(tr, iv, a.h, s_eps, a.S, i, x, tg);
             for (; i < a.S; ++i) {
                 rk_step<T, KIND, FAT, GROUPS>(tr, iv, a.scheme, a.h, s_eps[2 * i], s_eps[2 * i + 1], s_eps[2 * i + 2],
                                               s_eps + 2 * a.S + 1 + 4 * i, x, tg);
@@ -295,9 +313,10 @@ __global__ void FES_LAUNCH_BOUNDS fes_shoot_kernel(const ShootArgs<T> a) {
             tr, [&](int c) { return __ldg(trow + c * a.tB); }, [&](int c) { return __ldg(crow + c * a.cB); }, a.N,
             a.tile_off, iv);
     int i = 0;
-    if (a.scheme == 4)
-        for (; i + STEP_UNROLL <= a.S; i += STEP_UNROLL)
-            rk4_steps<T, KIND, FAT, GROUPS, STEP_UNROLL>(tr, iv, a.h, s_eps, a.S, i, x, tg);
+    constexpr int UNROLL = shoot_unroll<T, FAT, GROUPS>();
+    if constexpr (UNROLL > 1)
+        if (a.scheme == 4)
+            for (; i + UNROLL <= a.S; i += UNROLL) rk4_steps<T, KIND, FAT, GROUPS, UNROLL>(tr, iv, a.h, s_eps, a.S, i, x, tg);
     for (; i < a.S; ++i)
         rk_step<T, KIND, FAT, GROUPS>(tr, iv, a.scheme, a.h, s_eps[2 * i], s_eps[2 * i + 1], s_eps[2 * i + 2],
                                       s_eps + 2 * a.S + 1 + 4 * i, x, tg);

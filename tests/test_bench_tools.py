@@ -37,7 +37,8 @@ def test_static_counts_describe_the_built_library_and_cover_the_bench_kernels():
         inst = rec["fp64_inst"] if "double" in name else rec["fp32_inst"]
         assert inst > 50 and rec["mufu"] >= 4 and rec["registers"] <= 255, (name, rec)
     head = kernels[wanted[0]]
-    assert head["fp64_inst"] == 247 and head["registers"] == 164 and head["stack_bytes"] == 0
+    assert head["fp64_inst"] == 247 and head["registers"] <= 164 and head["stack_bytes"] == 0
+    assert head["steps_in_path"] == 2, "the trajectory kernels run RK4 steps in pairs (FES_IVP_UNROLL)"
     # the RK4 step of every kernel stays free of local-memory traffic except where DESIGN.md says so (LamCache, Hmed2018)
     dense = kernels[wanted[3]]
     assert dense["fp64_inst"] < 450, "the parameter columns of a fatigue model go through the 2 x 2 step propagator"
