@@ -20,6 +20,7 @@ FES_NP = 14
 FES_DIR_X0, FES_DIR_U, FES_DIR_P, FES_DIR_W, FES_DIR_PF = 1, 2, 4, 8, 16
 FES_TILE = 5
 FES_PARAMS_SHARED, FES_WIN_SHARED, FES_CTRL_SHARED, FES_TABLES_READY, FES_TARGET_SHARED = 1, 2, 4, 8, 16
+FES_STATIC_SCRATCH_BYTES = 4 * 1024 * 1024  # fes_shoot_static_f64: size of the library-owned static device scratch
 
 PARAM_NAMES = ("a_rest", "km_rest", "tau1_rest", "tau2", "alpha_a", "alpha_tau1", "alpha_km", "tau_fat",
                "pd0", "pdt", "ar", "bs", "Is", "cr")
@@ -81,6 +82,7 @@ PROTOTYPES = {
     "fes_ivp_f32": (c_int, [POINTER(FesDesc), POINTER(FesIvpBuffers), c_void_p]),
     "fes_shoot_f64": (c_int, [POINTER(FesDesc), POINTER(FesShootBuffers), c_void_p]),
     "fes_shoot_f32": (c_int, [POINTER(FesDesc), POINTER(FesShootBuffers), c_void_p]),
+    "fes_shoot_static_f64": (c_int, [POINTER(FesDesc), POINTER(FesShootBuffers), c_void_p]),
     "fes_ivp_host_f64": (c_int, [POINTER(FesDesc), POINTER(FesIvpBuffers), c_void_p]),
     "fes_ivp_host_f32": (c_int, [POINTER(FesDesc), POINTER(FesIvpBuffers), c_void_p]),
     "fes_shoot_host_f64": (c_int, [POINTER(FesDesc), POINTER(FesShootBuffers), c_void_p]),

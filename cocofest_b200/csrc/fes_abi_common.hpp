@@ -15,6 +15,7 @@ namespace abi {
 
 enum {
     E_OK = 0, E_DESC = -1, E_MODEL = -2, E_SIZE = -3, E_DIRS = -4, E_BUF = -5, E_WORKSPACE = -6, E_TRACE = -7,
+    E_STATIC_SCRATCH = -8,
 };
 
 inline int num_controls(int kind, int N) { return kind == FES_DING2007 ? 1 : (kind == FES_HMED2018 ? N : 0); }
@@ -211,6 +212,7 @@ inline const char *strerror_abi(int code) {
         case E_BUF: return "a required buffer is NULL";
         case E_WORKSPACE: return "workspace is NULL or smaller than fes_workspace_bytes";
         case E_TRACE: return "invalid trace request (trace_every must be 0, 1 or n_steps; trace_batch <= batch; trace buffer)";
+        case E_STATIC_SCRATCH: return "the tables of this call need more than FES_STATIC_SCRATCH_BYTES of scratch: use fes_shoot_f64 with a caller workspace";
     }
     return nullptr;
 }

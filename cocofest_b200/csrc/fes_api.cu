@@ -131,6 +131,48 @@ int ident_impl(const FesDesc *d, const FesIdentBuffers *b, const FesIdentOptions
     return rc;
 }
 
+// ---- fes_shoot_static_f64: the interval kernel with its tables in library-owned static device memory ----------------------
+// For callers that cannot allocate (stream capture, serving loops).  The scratch is a file-scope device array: every GPU that
+// loads the library holds FES_STATIC_SCRATCH_BYTES of it until the process exits.  In host code the name `g_static_scratch` is
+// only a handle for the runtime, NOT a device address: the address is asked for once per device, with that device current
+// (cudaGetSymbolAddress), and that pointer is what the kernels get.  All calls on a device share the array.
+static __device__ __align__(256) unsigned char g_static_scratch[FES_STATIC_SCRATCH_BYTES];
+
+std::mutex g_scratch_mu;
+void *g_scratch_ptr[64] = {};
+
+int static_scratch(void **out) {
+    int dev = 0;
+    int rc = (int)cudaGetDevice(&dev);
+    if (rc) return rc;
+    if (dev < 0 || dev >= 64) return (int)cudaErrorInvalidDevice;
+    std::lock_guard<std::mutex> lock(g_scratch_mu);
+    if (g_scratch_ptr[dev] == nullptr) {
+        void *ptr = nullptr;
+        rc = (int)cudaGetSymbolAddress(&ptr, g_static_scratch);
+        if (rc) return rc;
+        if (ptr == nullptr) return (int)cudaErrorInvalidSymbol;
+        g_scratch_ptr[dev] = ptr;
+    }
+    *out = g_scratch_ptr[dev];
+    return E_OK;
+}
+
+int shoot_static_impl(const FesDesc *d, const FesShootBuffers *b, void *stream) {
+    int rc = check_desc(d, false);
+    if (rc) return rc;
+    if (b == nullptr) return E_BUF;
+    const Carve c = carve(d, sizeof(double));
+    if ((int64_t)c.total > (int64_t)FES_STATIC_SCRATCH_BYTES) return E_STATIC_SCRATCH;
+    void *ptr = nullptr;
+    rc = static_scratch(&ptr);
+    if (rc) return rc;
+    FesShootBuffers g = *b;  // the caller's workspace fields are ignored
+    g.workspace = ptr;
+    g.workspace_bytes = FES_STATIC_SCRATCH_BYTES;
+    return shoot_impl<double>(d, &g, stream);
+}
+
 // ---- host-buffer variants: stream-ordered temporaries, H2D, kernels, D2H --------------------
 // The staging buffers come from a memory pool the LIBRARY owns (one per device, created on first use) whose release
 // threshold is unbounded: memory freed by one call stays mapped for the next one.  With the device's default pool
@@ -495,6 +537,7 @@ int fes_ivp_f64(const FesDesc *d, const FesIvpBuffers *b, void *s) { return ivp_
 int fes_ivp_f32(const FesDesc *d, const FesIvpBuffers *b, void *s) { return ivp_impl<float>(d, b, s); }
 int fes_shoot_f64(const FesDesc *d, const FesShootBuffers *b, void *s) { return shoot_impl<double>(d, b, s); }
 int fes_shoot_f32(const FesDesc *d, const FesShootBuffers *b, void *s) { return shoot_impl<float>(d, b, s); }
+int fes_shoot_static_f64(const FesDesc *d, const FesShootBuffers *b, void *s) { return shoot_static_impl(d, b, s); }
 int fes_ivp_host_f64(const FesDesc *d, const FesIvpBuffers *b, void *s) { return ivp_host_impl<double>(d, b, s); }
 int fes_ivp_host_f32(const FesDesc *d, const FesIvpBuffers *b, void *s) { return ivp_host_impl<float>(d, b, s); }
 int fes_shoot_host_f64(const FesDesc *d, const FesShootBuffers *b, void *s) { return shoot_host_impl<double>(d, b, s); }

@@ -178,6 +178,24 @@ int fes_ivp_f32(const FesDesc *desc, const FesIvpBuffers *buf, void *stream);
 int fes_shoot_f64(const FesDesc *desc, const FesShootBuffers *buf, void *stream);
 int fes_shoot_f32(const FesDesc *desc, const FesShootBuffers *buf, void *stream);
 
+/* fes_shoot_f64 for callers that must not allocate (CUDA graph capture, tight serving loops, harnesses that forbid
+ * cudaMalloc).  No counterpart in the reference.  The window
+ * tables and the stage table, which fes_shoot_f64 keeps in the caller's workspace, live in a static device array of
+ * FES_STATIC_SCRATCH_BYTES that every GPU which loads the library holds until the process exits; buf->workspace and
+ * buf->workspace_bytes are ignored, inputs and outputs are the caller's device buffers as in fes_shoot_f64, and the
+ * results are bit-identical to fes_shoot_f64's.  The call allocates and frees nothing (no cudaMalloc / cudaFree /
+ * pool): it launches the table kernel and the interval kernel on `stream` and returns.
+ *   - returns -8 (see fes_strerror) when fes_workspace_bytes(desc, 0) > FES_STATIC_SCRATCH_BYTES = 4 MiB: a shared
+ *     window (FES_WIN_SHARED) needs n_shooting * r + 6 n_steps + 1 doubles, r = 2 + 2 n_trunc for FES_HMED2018 or
+ *     FES_DIR_W and 2 otherwise; per-scenario windows need batch times the first term;
+ *   - ALL calls on a device share the array: calls that may overlap on the GPU (different streams, or graphs replayed
+ *     concurrently) race on it -- keep them on one stream or order them with events;
+ *   - the array keeps the last call's tables; every call rebuilds all it reads before reading it (nothing has to start
+ *     at zero), and FES_TABLES_READY is honoured only in that sense: set it only when the previous call through THIS
+ *     entry point on this device had the same (desc, stim_win). */
+#define FES_STATIC_SCRATCH_BYTES (4 * 1024 * 1024)
+int fes_shoot_static_f64(const FesDesc *desc, const FesShootBuffers *buf, void *stream);
+
 /* Force-tracking cost (fes_identification_ocp.py:248-266) with its gradient and Gauss-Newton matrix, and the
  * bounded Levenberg-Marquardt identification of the P-group parameters (fes_identification_ocp.py:269-299), one
  * thread per candidate, whole loop on device.  desc->dirs must be FES_DIR_P, desc->fatigue 0. */

@@ -283,6 +283,20 @@ int fes_ivp_f32(const FesDesc *d, const FesIvpBuffers *b, void *) { return ivp_i
 int fes_shoot_f64(const FesDesc *d, const FesShootBuffers *b, void *) { return shoot_impl<double>(d, b); }
 int fes_shoot_f32(const FesDesc *d, const FesShootBuffers *b, void *) { return shoot_impl<float>(d, b); }
 
+// the static-scratch entry point: here the "device" array is a static host array of the same size
+int fes_shoot_static_f64(const FesDesc *d, const FesShootBuffers *b, void *) {
+    alignas(256) static unsigned char scratch[FES_STATIC_SCRATCH_BYTES];
+    if (!d) return E_DESC;
+    if (!b) return E_BUF;
+    const int64_t wb = fes_workspace_bytes(d, 0);
+    if (wb < 0) return E_SIZE;
+    if (wb > (int64_t)FES_STATIC_SCRATCH_BYTES) return E_STATIC_SCRATCH;
+    FesShootBuffers bb = *b;
+    bb.workspace = scratch;
+    bb.workspace_bytes = FES_STATIC_SCRATCH_BYTES;
+    return shoot_impl<double>(d, &bb);
+}
+
 // host-buffer entry points: same loops, workspace allocated here
 #define HOST_VARIANT(name, impl, T, Buf)                                                      \
     int name(const FesDesc *d, const Buf *b, void *) {                                        \
