@@ -445,8 +445,10 @@ def main():
     try:  # dram bytes of one ncu --set full capture (scripts/ncu_traffic.py), valid only for the build it was taken from
         cap = json.loads((ROOT / "profiles" / "r02_ivp_x0_traffic.json").read_text())
         if cap.get("dtype", "f64") == args.dtype and cap.get("batch") == B and cap.get("final_time_s") == args.final_time:
-            if counts and cap.get("sass_sha256") == json.loads((_lib.LIB_PATH.parent / "sass_counts.json").read_text()).get("sass_sha256"):
-                traffic, traffic_src = cap.get("dram_bytes"), "profiles/r02_ivp_x0_traffic.json (ncu --set full of the same device code, sha256 of the SASS dump)"
+            # tied to the device code of THIS kernel (sha256 of its SASS, scripts/sass_count.py): other kernels of the
+            # library may come and go without orphaning the capture
+            if kc and cap.get("kernel_sass_sha256") and cap.get("kernel_sass_sha256") == kc.get("sass_sha256"):
+                traffic, traffic_src = cap.get("dram_bytes"), "profiles/r02_ivp_x0_traffic.json (ncu --set full of the same device code: sha256 of the kernel's SASS matches)"
             else:
                 traffic_src = "profiles/r02_ivp_x0_traffic.json was captured from another build of the library: dropped"
     except Exception:
@@ -493,7 +495,7 @@ def main():
     if world == 1 and not args.no_configs:
         del params_d, x0_d
         torch.cuda.empty_cache()
-        wanted = ["0", "1", "3", "4", "4c", "5", "5pf"]   # 5pf: the parameter columns of a fatigue model (reduced form, 2 x 2 propagator)
+        wanted = ["0", "1", "3", "4", "4c", "5", "5c", "5pf"]   # 5pf: the parameter columns of a fatigue model (reduced form, 2 x 2 propagator)
         configs, configs_meta = bc.run_configs(wanted, dev, "f64", steps=3, warmup=3, flush=flush)
         other = "f32" if not f32 else "f64"   # the headline workload in the other arithmetic type
         r2, _ = bc.run_configs(["2x0"], dev, other, steps=2, warmup=2, flush=flush, t2=args.final_time)

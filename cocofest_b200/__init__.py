@@ -6,7 +6,7 @@ Host side (Python/PyTorch) mirrors the reference surface for the hot path only:
 and the multiple-shooting defect / Jacobian evaluation; the arithmetic runs in hand-written sm_100a CUDA
 kernels behind the C ABI of ``include/fes_b200.h``.
 """
-from . import fes
+from . import fes, hill_coefficients
 from .models import (
     DingModelFrequency,
     DingModelFrequencyWithFatigue,
@@ -29,7 +29,7 @@ from .identification import (
 )
 
 __all__ = [
-    "fes", "FesModel", "ModelMaker", "OdeSolver", "IvpFes", "OcpFes", "FesShooting", "FesNmpcBatch", "FesIntegrator", "FourierSeries",
+    "fes", "hill_coefficients", "FesModel", "ModelMaker", "OdeSolver", "IvpFes", "OcpFes", "FesShooting", "FesNmpcBatch", "FesIntegrator", "FourierSeries",
     "DingModelFrequency", "DingModelFrequencyWithFatigue",
     "DingModelPulseWidthFrequency", "DingModelPulseWidthFrequencyWithFatigue",
     "DingModelPulseIntensityFrequency", "DingModelPulseIntensityFrequencyWithFatigue",

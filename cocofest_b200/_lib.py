@@ -18,6 +18,7 @@ FES_ABI_VERSION = 1
 FES_DING2003, FES_DING2007, FES_HMED2018 = 0, 1, 2
 FES_NP = 14
 FES_DIR_X0, FES_DIR_U, FES_DIR_P, FES_DIR_W, FES_DIR_PF = 1, 2, 4, 8, 16
+FES_DIR_C = 32  # shoot: the force factor fl * fv + fp of the interval as an input row of ctrl and a Jacobian column
 FES_TILE = 5
 FES_PARAMS_SHARED, FES_WIN_SHARED, FES_CTRL_SHARED, FES_TABLES_READY, FES_TARGET_SHARED = 1, 2, 4, 8, 16
 FES_STATIC_SCRATCH_BYTES = 4 * 1024 * 1024  # fes_shoot_static_f64: size of the library-owned static device scratch

@@ -30,6 +30,9 @@ inline int num_dirs(int kind, int fat, int dirs) {
         case FES_DIR_X0: return nx;
         case FES_DIR_X0 | FES_DIR_U: return nx + nu_t;
         case FES_DIR_U: return nu_t > 0 ? nu_t : -1;
+        case FES_DIR_X0 | FES_DIR_U | FES_DIR_C: return nx + nu_t + 1;
+        case FES_DIR_X0 | FES_DIR_C: return kind == FES_DING2003 ? nx + 1 : -1;
+        case FES_DIR_U | FES_DIR_C: return kind == FES_HMED2018 ? nu_t + 1 : -1;  // further intensity tiles of a factor call
         case FES_DIR_P: return np;
         case FES_DIR_P | FES_DIR_PF: return fat ? np + 4 : -1;
         case FES_DIR_W: return FES_TILE;
@@ -49,7 +52,7 @@ inline int check_desc(const FesDesc *d, bool ivp) {
     if (d->n_trunc < 1 || d->n_trunc > max_trunc || d->n_shooting < 1 || d->n_steps < 1 || d->n_steps > 256) return E_SIZE;
     if (d->batch < 1 || !(d->dt > 0.0) || !(d->tauc > 0.0)) return E_SIZE;
     if (num_dirs(d->model_kind, d->fatigue, d->dirs) < 0) return E_DIRS;
-    if (ivp && (d->dirs & (FES_DIR_U | FES_DIR_W))) return E_DIRS;
+    if (ivp && (d->dirs & (FES_DIR_U | FES_DIR_W | FES_DIR_C))) return E_DIRS;
     if (d->tile_offset < 0 || d->tile_offset >= d->n_trunc + FES_TILE) return E_SIZE;
     if (ivp) {
         if (d->trace_every != 0 && d->trace_every != 1 && d->trace_every != d->n_steps) return E_TRACE;
@@ -126,7 +129,7 @@ void fill_shoot_args(const FesDesc *d, const FesShootBuffers *b, const Carve &c,
     a.ctrl = (const T *)b->ctrl;
     a.cB = (d->flags & FES_CTRL_SHARED) ? 1 : d->batch;
     a.cS = (d->flags & FES_CTRL_SHARED) ? 0 : 1;
-    a.nu = num_controls(d->model_kind, d->n_trunc);
+    a.nu = num_controls(d->model_kind, d->n_trunc) + ((d->dirs & FES_DIR_C) ? 1 : 0);  // rows of ctrl per node
     a.G = (T *)b->G;
     a.Phi = (T *)b->Phi;
     a.J = (T *)b->J;

@@ -95,7 +95,7 @@ int shoot_impl(const FesDesc *d, const FesShootBuffers *b, void *stream) {
     int rc = check_desc(d, false);
     if (rc) return rc;
     if (b == nullptr || b->params == nullptr || b->X == nullptr) return E_BUF;
-    const int nu = num_controls(d->model_kind, d->n_trunc);
+    const int nu = num_controls(d->model_kind, d->n_trunc) + ((d->dirs & FES_DIR_C) ? 1 : 0);
     if (nu > 0 && b->ctrl == nullptr) return E_BUF;
     int groups = d->dirs;
     if (d->model_kind == FES_DING2003) groups &= ~FES_DIR_U;
@@ -335,7 +335,7 @@ int shoot_host_impl(const FesDesc *d, const FesShootBuffers *h, void *stream) {
     if (rc) return rc;
     if (h == nullptr || h->params == nullptr || h->X == nullptr || h->stim_win == nullptr) return E_BUF;
     cudaStream_t s = (cudaStream_t)stream;
-    const int nx = d->fatigue ? 5 : 2, nu = num_controls(d->model_kind, d->n_trunc);
+    const int nx = d->fatigue ? 5 : 2, nu = num_controls(d->model_kind, d->n_trunc) + ((d->dirs & FES_DIR_C) ? 1 : 0);
     if (nu > 0 && h->ctrl == nullptr) return E_BUF;
     const size_t B = (size_t)d->batch, ns = (size_t)d->n_shooting, N = (size_t)d->n_trunc;
     int groups = d->dirs;

@@ -37,7 +37,10 @@
 namespace fes {
 
 enum { DING2003 = 0, DING2007 = 1, HMED2018 = 2 };
-enum { G_X0 = 1, G_U = 2, G_P = 4, G_W = 8, G_PF = 16 };
+enum { G_X0 = 1, G_U = 2, G_P = 4, G_W = 8, G_PF = 16, G_C = 32 };
+// G_C: the force factor c = fl fv + fp of f_dot_fun (ding2003.py:309-311), F' = c (A q - F/(tau1 + tau2 q)), enters as a
+// per-interval input (the row after the model's own controls) and gets one tangent column d / d c.  Kernels without G_C
+// integrate c = 1 and do not execute a single instruction for it.
 constexpr int TILE = 5;
 constexpr int NP = 14;
 enum {
@@ -52,7 +55,8 @@ enum {
     D_WT,                                       // pulse time of a window slot
     D_A_REST, D_KM_REST, D_TAU1_REST, D_TAU2,   // identifiable parameters (fes_identification_ocp.py:269-299)
     D_PD0, D_PDT, D_AR, D_BS, D_IS, D_CR,
-    D_ALPHA_A, D_ALPHA_TAU1, D_ALPHA_KM, D_TAU_FAT
+    D_ALPHA_A, D_ALPHA_TAU1, D_ALPHA_KM, D_TAU_FAT,
+    D_FC                                        // the force factor c of the interval (G_C)
 };
 
 template <int KIND, bool FAT, int GROUPS>
@@ -60,10 +64,12 @@ struct Dirs {
     static constexpr int NX = FAT ? 5 : 2;
     static constexpr int n_x0 = (GROUPS & G_X0) ? NX : 0;
     static constexpr int n_u = (GROUPS & G_U) ? (KIND == DING2007 ? 1 : (KIND == HMED2018 ? TILE : 0)) : 0;
+    static constexpr int n_c = (GROUPS & G_C) ? 1 : 0;
     static constexpr int n_p = (GROUPS & G_P) ? (KIND == DING2003 ? 4 : (KIND == DING2007 ? 6 : 8)) : 0;
     static constexpr int n_pf = ((GROUPS & G_PF) && FAT) ? 4 : 0;
     static constexpr int n_w = (GROUPS & G_W) ? TILE : 0;
-    static constexpr int ND = n_x0 + n_u + n_p + n_pf + n_w;
+    static constexpr int ND = n_x0 + n_u + n_c + n_p + n_pf + n_w;
+    static constexpr bool FC = (GROUPS & G_C) != 0;
     // window tables carry per-slot weights (not only their sums)
     static constexpr bool SLOT = (KIND == HMED2018) || (GROUPS & G_W);
 
@@ -72,6 +78,8 @@ struct Dirs {
         d -= n_x0;
         if (d < n_u) return KIND == DING2007 ? D_PW : D_INT;
         d -= n_u;
+        if (d < n_c) return D_FC;
+        d -= n_c;
         if (d < n_p) {
             if (d < 4) return D_A_REST + d;
             return KIND == DING2007 ? D_PD0 + (d - 4) : D_AR + (d - 4);
@@ -83,7 +91,7 @@ struct Dirs {
     // window-slot index inside the tile for D_INT / D_WT columns
     static constexpr int slot(int d) {
         if (d >= n_x0 && d < n_x0 + n_u) return d - n_x0;
-        return d - (n_x0 + n_u + n_p + n_pf);
+        return d - (n_x0 + n_u + n_c + n_p + n_pf);
     }
 };
 
@@ -277,6 +285,7 @@ template <typename T, int ND>
 struct Interval {
     T E;                       // Cn forcing amplitude: S(t) = E * eps(t - t_k)
     T g;                       // pulse-width scaling of A (ding2007), 1 otherwise
+    T fc;                      // force factor fl fv + fp of the interval (G_C), 1 otherwise
     T sE[ND > 0 ? ND : 1];     // d E / d direction
     T dg[ND > 0 ? ND : 1];     // d g / d direction
 };
@@ -309,6 +318,8 @@ FES_HD void interval_setup(const Traj<T> &tr, TF tab, CF ctl, int N, int tile_of
         iv.dg[d] = T(0);
     });
     iv.g = T(1);
+    iv.fc = T(1);
+    if constexpr (D::FC) iv.fc = ctl(KIND == DING2007 ? 1 : (KIND == HMED2018 ? N : 0));  // the row after the model's controls
     if constexpr (KIND == DING2007) {
         // a_calculation, ding2007.py:188; the control is the width of the LAST pulse (ding2007.py:280)
         const T pw = ctl(0);
@@ -389,10 +400,12 @@ template <typename T>
 struct Stage {  // the non-trivial entries of d f / d (x, params) at a stage point
     T cF, cCn, cKm, cT1, cA, cT2, cG, dA, dT1, dKm;
     T cW;  // fatigue: d F' / d W = cA alpha_a + cT1 alpha_tau1 + cKm alpha_km  (reduced columns)
+    T fU;  // G_C: F' / c, the forcing of the d / d c column
 };
 
-template <typename T, int KIND, bool FAT, bool NEED>
-FES_HD void nominal_rhs(const Traj<T> &tr, T Ee, T g, const T *x, T *k, Stage<T> &st) {
+// FC: the F row and every entry of its Jacobian carry the interval's force factor fc (f_dot_fun, ding2003.py:309-311)
+template <typename T, int KIND, bool FAT, bool NEED, bool FC = false>
+FES_HD void nominal_rhs(const Traj<T> &tr, T Ee, T g, const T *x, T *k, Stage<T> &st, T fc = T(1)) {
     const T cn = x[0], f = x[1];
     const T A = FAT ? x[2] : tr.a_rest;
     const T t1 = FAT ? x[3] : tr.tau1_rest;
@@ -402,9 +415,13 @@ FES_HD void nominal_rhs(const Traj<T> &tr, T Ee, T g, const T *x, T *k, Stage<T>
     const T M = xfma(tr.tau2, cn, t1 * s);  // (tau1 + tau2 q) * s
     const T r = xrcp(s * M);
     const T is = r * M;                      // 1 / (Km + Cn)
-    const T invD = s * (r * s);              // 1 / (tau1 + tau2 q)
+    const T invD1 = s * (r * s);             // 1 / (tau1 + tau2 q)
     const T q = cn * is;
-    const T Aeff = (KIND == DING2007) ? A * g : A;
+    const T Aeff1 = (KIND == DING2007) ? A * g : A;
+    if constexpr (FC && NEED) st.fU = xfma(Aeff1, q, -(f * invD1));
+    // with a force factor the two coefficients of the F row carry it, and with them every Jacobian entry below
+    const T invD = FC ? invD1 * fc : invD1;  // c / (tau1 + tau2 q)
+    const T Aeff = FC ? Aeff1 * fc : Aeff1;
     k[1] = xfma(Aeff, q, -(f * invD));
     if constexpr (FAT) {
         k[2] = xfma(tr.alpha_a, f, xfma(-tr.kappa, A, tr.a_rest_k));
@@ -413,7 +430,7 @@ FES_HD void nominal_rhs(const Traj<T> &tr, T Ee, T g, const T *x, T *k, Stage<T>
     }
     if constexpr (NEED) {
         st.cF = -invD;
-        const T ct1 = f * invD * invD;       // d F' / d tau1
+        const T ct1 = f * invD * invD1;      // d F' / d tau1
         st.cT1 = ct1;
         const T Gc = xfma(ct1, tr.tau2, Aeff);  // d F' / d q
         const T u = Gc * is;                    // d q / d Cn = (1 - q)/(Km + Cn),  d q / d Km = -q/(Km + Cn)
@@ -422,6 +439,10 @@ FES_HD void nominal_rhs(const Traj<T> &tr, T Ee, T g, const T *x, T *k, Stage<T>
         st.cA = (KIND == DING2007) ? q * g : q;
         st.cT2 = ct1 * q;
         st.cG = A * q;
+        if constexpr (FC) {
+            st.cA *= fc;
+            st.cG *= fc;
+        }
         if constexpr (FAT) {
             st.cW = xfma(st.cA, tr.alpha_a, xfma(st.cT1, tr.alpha_tau1, st.cKm * tr.alpha_km));
             st.dA = (A - tr.a_rest) * tr.kappa2;   // d/d tau_fat of -(A - A_rest)/tau_fat
@@ -452,6 +473,7 @@ FES_HD void column_rhs(const Traj<T> &tr, const Stage<T> &st, T eps, T sE, T dg,
     if constexpr (CODE == D_TAU1_REST) kf += st.cT1;
     if constexpr (CODE == D_KM_REST) kf += st.cKm;
     if constexpr (CODE == D_TAU2) kf += st.cT2;
+    if constexpr (CODE == D_FC) kf += st.fU;
     if constexpr (dir_has_dg(CODE)) kf = xfma(st.cG, dg, kf);
     k[1] = kf;
 }
@@ -484,6 +506,7 @@ FES_HD void column_rhs_red(const Traj<T> &tr, const Stage<T> &st, T eps, T sE, T
         k[4] = xfma(-tr.kappa, v[4], st.dKm);
     }
     if constexpr (CODE == D_TAU2) kf += st.cT2;
+    if constexpr (CODE == D_FC) kf += st.fU;
     if constexpr (dir_has_dg(CODE)) kf = xfma(st.cG, dg, kf);
     k[1] = kf;
     k[2] = xfma(-tr.kappa, v[2], v[1]);
@@ -679,7 +702,7 @@ FES_HD void rk_step_scheme(const Traj<T> &tr, const Interval<T, Dirs<KIND, FAT, 
         const T ha = h * T(LAST ? 0.0 : TB::alpha(s + 1));
         {
             T k[NX];
-            nominal_rhs<T, KIND, FAT, NEED>(tr, T(0), iv.g, xs, k, st);  // k[0] is not used: Cn rides on the stage table
+            nominal_rhs<T, KIND, FAT, NEED, D::FC>(tr, T(0), iv.g, xs, k, st, iv.fc);  // k[0] is not used: Cn rides on the stage table
             if constexpr (FAT) {  // before xs[1] moves on: Wn' at this stage (k[2..4] of nominal_rhs are dead here)
                 const T kw = s == 0 ? xs[1] : xfma(-tr.kappa, wn_s, xs[1]);
                 if constexpr (TB::beta(s) != 0.0) wn_n = s == 0 ? hb * kw : xfma(hb, kw, wn_n);
@@ -801,6 +824,7 @@ FES_HD void rk_step_scheme(const Traj<T> &tr, const Interval<T, Dirs<KIND, FAT, 
                 if constexpr (C == D_TAU1_REST) acc = xfma(W[q], sq[q].cT1, acc);
                 if constexpr (C == D_KM_REST) acc = xfma(W[q], sq[q].cKm, acc);
                 if constexpr (C == D_TAU2) acc = xfma(W[q], sq[q].cT2, acc);
+                if constexpr (C == D_FC) acc = xfma(W[q], sq[q].fU, acc);
             });
             if constexpr (dir_has_dg(C)) acc = xfma(WGsum, iv.dg[d], acc);
             tg.V[d][1] = acc;
@@ -898,8 +922,9 @@ FES_HD void rk_step_scheme(const Traj<T> &tr, const Interval<T, Dirs<KIND, FAT, 
             if constexpr (dirs_have<D>(D_ALPHA_TAU1)) nsum([&](int s) { return sq[s].cT1; }, nT1F, nT1W);
             if constexpr (dirs_have<D>(D_ALPHA_KM)) nsum([&](int s) { return sq[s].cKm; }, nKmF, nKmW);
         }
-        T sT2F = T(0), sT2W = T(0);
+        T sT2F = T(0), sT2W = T(0), sFcF = T(0), sFcW = T(0);
         if constexpr (dirs_have<D>(D_TAU2)) wsum([&](auto q) { return sq[decltype(q)::value].cT2; }, sT2F, sT2W);
+        if constexpr (dirs_have<D>(D_FC)) wsum([&](auto q) { return sq[decltype(q)::value].fU; }, sFcF, sFcW);
         // d / d tau_fat: the three rows are forced by (x - x_rest)/tau_fat^2 = kappa^2 (d_X fm(t) + alpha_X Wn(t)), hence
         //     m_X(s) = m_X fm_s + kappa^2 (d_X sigma_s + alpha_X omega_s),
         // sigma / omega = the scheme's stage values of y' = -y/tau_fat + fm(t) | + Wn(t) from 0 (sigma is loop-invariant).
@@ -970,6 +995,10 @@ FES_HD void rk_step_scheme(const Traj<T> &tr, const Interval<T, Dirs<KIND, FAT, 
             if constexpr (C == D_TAU2) {
                 aF += sT2F;
                 aW += sT2W;
+            }
+            if constexpr (C == D_FC) {
+                aF += sFcF;
+                aW += sFcW;
             }
             if constexpr (dir_own_m(C)) {
                 const T mA = tg.V[d][0], mT1 = tg.V[d][3], mKm = tg.V[d][4], k2 = tr.kappa2;

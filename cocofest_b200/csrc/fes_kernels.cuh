@@ -67,7 +67,8 @@ constexpr int min_blocks() {
 #endif
     // same effect on the two-state kernels (Hmed P columns: 182 registers unconstrained, +16 % under the 204 cap,
     // profiles/r01_tune_ident_g.txt); the dense fatigue parameter columns (P, P|PF: 204-254 registers) stay free
-    constexpr bool red = FAT && (GROUPS == G_X0 || GROUPS == G_U || GROUPS == G_W || (GROUPS == (G_X0 | G_U) && KIND == DING2007));
+    constexpr int G0 = GROUPS & ~G_C;  // the force-factor column rides with the X0 | U sets and follows their policy
+    constexpr bool red = FAT && (G0 == G_X0 || G0 == G_U || G0 == G_W || (G0 == (G_X0 | G_U) && KIND == DING2007));
     // Ding2007 parameter columns (config 3): 7 resident blocks = 120 registers, no spill, +4 % over the 138-register build;
     // every other kernel moved by < 1.5 % or lost (profiles/r01_tune_min_blocks_m.txt)
     if (sizeof(T) == 8 && !FAT && KIND == DING2007 && GROUPS == G_P) return 7;
@@ -397,6 +398,15 @@ int launch_shoot_kf(int groups, const ShootArgs<T> &a, cudaStream_t s) {
             else return launch_shoot_t<T, KIND, FAT, G_X0>(a, s);
         case G_U:
             if constexpr (KIND != DING2003) return launch_shoot_t<T, KIND, FAT, G_U>(a, s);
+            else return ERR_DIRS;
+        case G_X0 | G_U | G_C:  // with the force factor of the interval as an input and a column (FES_DIR_C)
+            if constexpr (KIND != DING2003) return launch_shoot_t<T, KIND, FAT, G_X0 | G_U | G_C>(a, s);
+            else return launch_shoot_t<T, KIND, FAT, G_X0 | G_C>(a, s);
+        case G_X0 | G_C:
+            if constexpr (KIND == DING2003) return launch_shoot_t<T, KIND, FAT, G_X0 | G_C>(a, s);
+            else return ERR_DIRS;
+        case G_U | G_C:  // Hmed2018: the intensity tiles after the first of a call that carries the force factor
+            if constexpr (KIND == HMED2018) return launch_shoot_t<T, KIND, FAT, G_U | G_C>(a, s);
             else return ERR_DIRS;
         case G_P: return launch_shoot_t<T, KIND, FAT, G_P>(a, s);
         case G_P | G_PF:

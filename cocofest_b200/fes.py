@@ -21,7 +21,7 @@ import numpy as np
 import torch
 
 from . import _lib
-from ._lib import (FES_CTRL_SHARED, FES_DING2003, FES_DING2007, FES_DIR_P, FES_DIR_PF, FES_DIR_U, FES_DIR_W,
+from ._lib import (FES_CTRL_SHARED, FES_DING2003, FES_DING2007, FES_DIR_C, FES_DIR_P, FES_DIR_PF, FES_DIR_U, FES_DIR_W,
                    FES_DIR_X0, FES_HMED2018, FES_NP, FES_PARAMS_SHARED, FES_TARGET_SHARED, FES_TILE, FES_WIN_SHARED,
                    PARAM_INDEX, PARAM_NAMES, FesDesc, FesIdentBuffers, FesIdentOptions, FesIvpBuffers, FesShootBuffers)
 
@@ -140,8 +140,9 @@ def _desc(kind, fatigue, scheme, N, ns, S, dirs, flags, B, dt, t_start, tauc, r0
                    float(t_start), float(DEFAULT_TAUC[kind] if tauc is None else tauc), float(r0_km))
 
 
-def _common(kind, fatigue, params, win, ctrl, lead, dtype, N_expected=None):
-    """Normalises params / win / ctrl, derives (device, dtype, B, N, flags)."""
+def _common(kind, fatigue, params, win, ctrl, lead, dtype, N_expected=None, extra_ctrl_rows=0):
+    """Normalises params / win / ctrl, derives (device, dtype, B, N, flags).  extra_ctrl_rows: rows of ctrl after the
+    model's own controls (the force factor of a shoot call)."""
     lead = torch.as_tensor(lead)
     device = lead.device
     if dtype is None:
@@ -163,7 +164,7 @@ def _common(kind, fatigue, params, win, ctrl, lead, dtype, N_expected=None):
     elif win.dim() != 3 or win.shape[2] != B:
         raise ValueError("stim window must be [rows, N] or [rows, N, B]")
     N = win.shape[1]
-    nu = _nu(kind, N)
+    nu = _nu(kind, N) + extra_ctrl_rows
     if nu:
         if ctrl is None:
             raise ValueError("this model needs controls (last_pulse_width [ns,1] / pulse_intensity [ns,N])")
@@ -359,12 +360,21 @@ class ShootResult:
     Jp: torch.Tensor | None     # [ns, nx, np, B]      dPhi_k / d identifiable params (+ fatigue params)
     Jw: torch.Tensor | None     # [ns, nx, N, B]       dPhi_k / d window pulse times
     p_columns: tuple
+    Jc: torch.Tensor | None = None   # [ns, nx, B]     dPhi_k / d force factor of the interval (force_factor calls)
 
 
-def _shoot_layout(kind, fatigue, nx, nu, N, want):
+def _shoot_layout(kind, fatigue, nx, nu, N, want, factor=False):
     """Column counts of the Jacobian blocks (x, u, p, w), the names of the p columns and the kernel passes
-    [(dirs, tile_offset, first column)] that fill them."""
+    [(dirs, tile_offset, first column)] that fill them.  factor: the call carries the force factor; the blocks are x, u and
+    ONE more column d / d factor right after them (every pass writes its own columns and then that column: each pass
+    overwrites the previous one's copy with the same number, the last one leaves it in place)."""
     tiles = lambda n: (n + FES_TILE - 1) // FES_TILE
+    if factor:
+        cu = (1 if kind == FES_DING2007 else tiles(nu) * FES_TILE) if nu else 0
+        passes = [(FES_DIR_X0 | FES_DIR_U | FES_DIR_C, 0, 0)]
+        for t in range(1, tiles(nu) if kind == FES_HMED2018 else 1):
+            passes.append((FES_DIR_U | FES_DIR_C, t * FES_TILE, nx + t * FES_TILE))
+        return nx, cu, 0, 0, (), passes
     cx = nx if "x" in want else 0
     cu = (1 if kind == FES_DING2007 else tiles(nu) * FES_TILE) if "u" in want else 0
     np_cols = P_COLUMNS[kind] + (PF_COLUMNS if "pf" in want else ()) if "p" in want else ()
@@ -402,15 +412,42 @@ def _normalise_want(kind, fatigue, nu, want):
     return want
 
 
+def _with_factor(ctrl, force_factor, nu, ns, B, dtype, device):
+    """[ns, nu + 1, B]: the model's controls followed by the force factor of the interval."""
+    f = _prep(force_factor, dtype, device)
+    if f.dim() == 1:
+        f = f[:, None].expand(-1, B)
+    if f.dim() != 2 or f.shape[0] < ns or f.shape[1] != B:
+        raise ValueError("force_factor must be [ns] or [ns, B]")
+    rows = [f[:ns, None, :]]
+    if nu:
+        if ctrl is None:
+            raise ValueError("this model needs controls (last_pulse_width [ns,1] / pulse_intensity [ns,N])")
+        c = _prep(ctrl, dtype, device)
+        if c.dim() == 2:
+            c = c[:, :, None].expand(-1, -1, B)
+        if c.dim() != 3 or c.shape[0] < ns or c.shape[1] != nu or c.shape[2] != B:
+            raise ValueError("controls must be [ns, nu] or [ns, nu, B]")
+        rows.insert(0, c[:ns])
+    return torch.cat(rows, dim=1).contiguous()
+
+
 def shoot(kind, fatigue, params, X, win, dt, n_steps=10, ctrl=None, scheme=4, want=("x",), t_start=0.0, tauc=None,
-          r0_km=R0_KM_RELATIONSHIP, defects=True, endpoints=False, dtype=None) -> ShootResult:
+          r0_km=R0_KM_RELATIONSHIP, defects=True, endpoints=False, dtype=None, force_factor=None) -> ShootResult:
     """All intervals of all scenarios at once.
 
     X [ns+1, nx, B];  params [14] | [14,B];  win [>=ns,N] | [>=ns,N,B];  ctrl None | [ns,nu] | [ns,nu,B].
     want: subset of {"x", "u", "p", "pf", "w"} selecting the Jacobian blocks.
+    force_factor None | [ns] | [ns,B]: ``force_length * force_velocity + passive_force`` of ``f_dot_fun``
+    (ding2003.py:309-311), held constant over each interval -- the seam for a caller that integrates the joint dynamics
+    of an FES-MSK model itself.  Such a call returns Jx, Ju and Jc = dPhi_k / d factor_k (want is ignored).
     """
     X = torch.as_tensor(X)
-    device, dtype, B, N, flags, params, win, ctrl = _common(kind, fatigue, params, win, ctrl, X, dtype)
+    factor = force_factor is not None
+    if factor:
+        Xt = _prep(X, dtype if dtype is not None else (X.dtype if X.dtype in (torch.float32, torch.float64) else torch.float64), X.device)
+        ctrl = _with_factor(ctrl, force_factor, _nu(kind, torch.as_tensor(win).shape[1]), Xt.shape[0] - 1, Xt.shape[-1], Xt.dtype, Xt.device)
+    device, dtype, B, N, flags, params, win, ctrl = _common(kind, fatigue, params, win, ctrl, X, dtype, extra_ctrl_rows=int(factor))
     nx, nu = _nx(fatigue), _nu(kind, N)
     X = _prep(X, dtype, device)
     ns = X.shape[0] - 1
@@ -418,9 +455,9 @@ def shoot(kind, fatigue, params, X, win, dt, n_steps=10, ctrl=None, scheme=4, wa
         raise ValueError(f"X must be [ns+1, {nx}, B]")
     if win.shape[0] < ns or (ctrl is not None and ctrl.shape[0] < ns):
         raise ValueError("stim window / controls have fewer rows than n_shooting")
-    want = _normalise_want(kind, fatigue, nu, want)
-    cx, cu, cp, cw, np_cols, passes = _shoot_layout(kind, fatigue, nx, nu, N, want)
-    cols = cx + cu + cp + cw
+    want = {"x", "u"} if factor else _normalise_want(kind, fatigue, nu, want)
+    cx, cu, cp, cw, np_cols, passes = _shoot_layout(kind, fatigue, nx, nu, N, want, factor)
+    cols = cx + cu + cp + cw + int(factor)
 
     L = _lib.lib()
     is32 = dtype == torch.float32
@@ -429,8 +466,11 @@ def shoot(kind, fatigue, params, X, win, dt, n_steps=10, ctrl=None, scheme=4, wa
         # and copy each result back once (the host entry point would move the whole J both ways at every pass)
         dev = torch.device("cuda", torch.cuda.current_device())
         up = lambda t: None if t is None else t.to(dev, non_blocking=True)
-        r = shoot(kind, fatigue, up(params), up(X), up(win), dt, n_steps=n_steps, ctrl=up(ctrl), scheme=scheme, want=want,
-                  t_start=t_start, tauc=tauc, r0_km=r0_km, defects=defects, endpoints=endpoints, dtype=dtype)
+        cc, ff = ctrl, None
+        if factor:  # the recursive call puts the two parts together again
+            cc, ff = (ctrl[:, :nu].contiguous() if nu else None), ctrl[:, nu].contiguous()
+        r = shoot(kind, fatigue, up(params), up(X), up(win), dt, n_steps=n_steps, ctrl=up(cc), scheme=scheme, want=want,
+                  t_start=t_start, tauc=tauc, r0_km=r0_km, defects=defects, endpoints=endpoints, dtype=dtype, force_factor=up(ff))
 
         def down(t):
             if t is None:
@@ -439,7 +479,7 @@ def shoot(kind, fatigue, params, X, win, dt, n_steps=10, ctrl=None, scheme=4, wa
             h.copy_(t, non_blocking=True)
             return h
 
-        out = ShootResult(down(r.G), down(r.Phi), down(r.Jx), down(r.Ju), down(r.Jp), down(r.Jw), r.p_columns)
+        out = ShootResult(down(r.G), down(r.Phi), down(r.Jx), down(r.Ju), down(r.Jp), down(r.Jw), r.p_columns, down(r.Jc))
         torch.cuda.current_stream(dev).synchronize()
         return out
 
@@ -480,7 +520,8 @@ def shoot(kind, fatigue, params, X, win, dt, n_steps=10, ctrl=None, scheme=4, wa
     Jp = J[:, :, o:o + cp] if cp else None
     o += cp
     Jw = J[:, :, o:o + N] if cw else None
-    return ShootResult(G, Phi, Jx, Ju, Jp, Jw, tuple(np_cols))
+    Jc = J[:, :, cx + cu] if factor else None
+    return ShootResult(G, Phi, Jx, Ju, Jp, Jw, tuple(np_cols), Jc)
 
 
 class ShootPlan:
@@ -498,24 +539,28 @@ class ShootPlan:
     """
 
     def __init__(self, kind, fatigue, params, win, dt, n_shooting, batch, n_steps=10, ctrl=None, scheme=4, want=("x",),
-                 t_start=0.0, tauc=None, r0_km=R0_KM_RELATIONSHIP, defects=True, endpoints=False, dtype=torch.float64):
+                 t_start=0.0, tauc=None, r0_km=R0_KM_RELATIONSHIP, defects=True, endpoints=False, dtype=torch.float64,
+                 force_factor=False):
+        """force_factor=True: the calls carry the force factor fl * fv + fp of every interval (see ``shoot``) as ONE MORE ROW
+        of ``ctrl`` after the model's own controls -- ctrl is [ns, nu + 1, B] -- and return Jx, Ju and Jc (want is ignored)."""
         win = torch.as_tensor(win)
         device = win.device
         if device.type != "cuda" and not _lib.is_host_emulation():   # (the test suite's host build takes host pointers)
             raise ValueError("ShootPlan works on CUDA tensors (use shoot() for host tensors)")
         lead = torch.empty((1, int(batch)), dtype=dtype, device=device)
-        _, _, B, N, flags, params, win, ctrl = _common(kind, fatigue, params, win, ctrl, lead, dtype)
+        self.factor = bool(force_factor)
+        _, _, B, N, flags, params, win, ctrl = _common(kind, fatigue, params, win, ctrl, lead, dtype, extra_ctrl_rows=int(self.factor))
         self.kind, self.fatigue, self.dtype, self.device = kind, bool(fatigue), dtype, device
         self.B, self.N, self.ns, self.nx, self.nu = B, N, int(n_shooting), _nx(fatigue), _nu(kind, N)
         if win.shape[0] < self.ns:
             raise ValueError("stim window has fewer rows than n_shooting")
-        if self.nu and ctrl is None:
+        if (self.nu or self.factor) and ctrl is None:
             raise ValueError("this model needs controls: pass a template `ctrl` of the shape later calls will use")
         self._params, self._win, self._ctrl = params, win, ctrl
-        want = _normalise_want(kind, fatigue, self.nu, want)
-        cx, cu, cp, cw, self.p_columns, passes = _shoot_layout(kind, fatigue, self.nx, self.nu, N, want)
+        want = {"x", "u"} if self.factor else _normalise_want(kind, fatigue, self.nu, want)
+        cx, cu, cp, cw, self.p_columns, passes = _shoot_layout(kind, fatigue, self.nx, self.nu, N, want, self.factor)
         self._cols = (cx, cu, cp, cw)
-        cols = cx + cu + cp + cw
+        cols = cx + cu + cp + cw + int(self.factor)
         ns, nx = self.ns, self.nx
         self.G = torch.empty((ns, nx, B), dtype=dtype, device=device) if defects else None
         self.Phi = torch.empty((ns, nx, B), dtype=dtype, device=device) if endpoints else None
@@ -557,7 +602,7 @@ class ShootPlan:
 
         if X.dtype != self.dtype or X.device != self.device or tuple(X.shape) != (ns + 1, nx, B) or not X.is_contiguous():
             raise ValueError(f"X: expected a contiguous {self.dtype} tensor of shape {(ns + 1, nx, B)} on {self.device}")
-        ctrl = check(ctrl, self._ctrl, "ctrl") if self.nu else None
+        ctrl = check(ctrl, self._ctrl, "ctrl") if (self.nu or self.factor) else None
         params = check(params, self._params, "params")
         stream = ctypes.c_void_p(_stream_ptr(self.device))
         with self._on_device():
@@ -578,7 +623,8 @@ class ShootPlan:
         Jp = J[:, :, o:o + cp] if cp else None
         o += cp
         Jw = J[:, :, o:o + self.N] if cw else None
-        return ShootResult(self.G, self.Phi, Jx, Ju, Jp, Jw, self.p_columns)
+        Jc = J[:, :, cx + cu] if self.factor else None
+        return ShootResult(self.G, self.Phi, Jx, Ju, Jp, Jw, self.p_columns, Jc)
 
 
 @dataclass

@@ -73,6 +73,11 @@ extern "C" {
 #define FES_DIR_P 4   /* d / d identifiable parameters: a_rest, km_rest, tau1_rest, tau2 [, pd0, pdt | ar, bs, Is, cr] */
 #define FES_DIR_W 8   /* d / d pulse times of the window: FES_TILE columns from tile_offset                 */
 #define FES_DIR_PF 16 /* with FES_DIR_P, fatigue models: + alpha_a, alpha_tau1, alpha_km, tau_fat          */
+#define FES_DIR_C 32  /* shoot only, with X0|U (FES_HMED2018 also U alone, for the intensity tiles after the first): the force factor c = fl*fv + fp of f_dot_fun (ding2003.py:309-311),
+                       * F' = c (A q - F/(tau1 + tau2 q)), is an INPUT -- ctrl carries one more row per node after the model's
+                       * own controls, [ns][nu+1][B], holding c of the interval -- and J gets one column d Phi / d c after
+                       * the U columns.  The reference evaluates fl, fv, fp from the joint states inside the same ODE
+                       * (FES-MSK models); a caller that integrates the joint dynamics itself passes their values here. */
 #define FES_TILE 5
 
 /* flags */
@@ -122,7 +127,7 @@ typedef struct FesShootBuffers {
     const void *params;     /* [FES_NP][B] | [FES_NP]                 */
     const void *X;          /* [ns+1][nx][B]  decision states at nodes */
     const double *stim_win; /* [>=ns][N][B] | [>=ns][N]               */
-    const void *ctrl;       /* [ns][nu][B] | [ns][nu] | NULL          */
+    const void *ctrl;       /* [ns][nu][B] | [ns][nu] | NULL; nu + 1 rows with FES_DIR_C */
     void *G;                /* [ns][nx][B]  g_k = x_{k+1} - Phi_k  | NULL */
     void *Phi;              /* [ns][nx][B]  end point of every interval | NULL */
     void *J;                /* [ns][nx][j_cols][B], this call fills columns j_col0 .. j_col0+nd-1 | NULL when dirs = 0 */
@@ -165,7 +170,7 @@ int fes_version(void);
 const char *fes_strerror(int code);
 
 /* nx of a model; number of sensitivity columns of a direction set (< 0: unsupported set).
- * Supported sets: 0, X0, X0|U, U, P, P|PF, W   (ivp: 0, X0, P, P|PF). */
+ * Supported sets: 0, X0, X0|U, X0|U|C, U, U|C (FES_HMED2018), P, P|PF, W   (ivp: 0, X0, P, P|PF). */
 int fes_num_states(int fatigue);
 int fes_num_controls(int model_kind, int n_trunc);
 int fes_num_dirs(int model_kind, int fatigue, int dirs);

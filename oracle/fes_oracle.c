@@ -111,8 +111,9 @@ static inline dual d_tanh(dual a, int nd) { dual r; r.v = tanh(a.v); double s = 
 static inline dual d_scale(dual a, double c, int nd) { dual r; r.v = a.v * c; ND_LOOP r.d[k_] = a.d[k_] * c; return r; }
 static inline dual d_addc(dual a, double c, int nd) { dual r = a; (void)nd; r.v += c; return r; }
 
+/* fc: the force factor fl*fv + fp of f_dot_fun (ding2003.py:309-311), NULL = the default arguments (1 * 1 + 0) */
 static void rhs_dual(int kind, int fatigue, int N, dual t, const dual *x, const dual *u, const dual *p,
-                     const dual *win, double tauc, double r0_km, dual *xdot, int nd)
+                     const dual *win, double tauc, double r0_km, dual *xdot, int nd, const dual *fc)
 {
     dual r0 = d_addc(p[P_KM_REST], r0_km, nd);
     dual s = d_const(0.0, nd);
@@ -139,6 +140,7 @@ static void rhs_dual(int kind, int fatigue, int N, dual t, const dual *x, const 
     }
     dual q = d_div(cn, d_add(km, cn, nd), nd);
     xdot[1] = d_sub(d_mul(a, q, nd), d_div(f, d_add(tau1, d_mul(p[P_TAU2], q, nd), nd), nd), nd);
+    if (fc) xdot[1] = d_mul(xdot[1], *fc, nd);
     if (fatigue) {
         xdot[2] = d_add(d_div(d_neg(d_sub(x[2], p[P_A_REST], nd), nd), p[P_TAU_FAT], nd), d_mul(p[P_ALPHA_A], f, nd), nd);
         xdot[3] = d_add(d_div(d_neg(d_sub(x[3], p[P_TAU1_REST], nd), nd), p[P_TAU_FAT], nd), d_mul(p[P_ALPHA_TAU1], f, nd), nd);
@@ -147,27 +149,27 @@ static void rhs_dual(int kind, int fatigue, int N, dual t, const dual *x, const 
 }
 
 static void interval_dual(int kind, int fatigue, int scheme, int N, int S, double t0, double dt, dual *x,
-                          const dual *u, const dual *p, const dual *win, double tauc, double r0_km, int nd)
+                          const dual *u, const dual *p, const dual *win, double tauc, double r0_km, int nd, const dual *fc)
 {
     int nx = fatigue ? 5 : 2;
     double h = dt / S;
     dual k1[5], k2[5], k3[5], k4[5], xs[5];
     for (int i = 1; i <= S; ++i) {
         double t = t0 + h * (i - 1);
-        rhs_dual(kind, fatigue, N, d_const(t, nd), x, u, p, win, tauc, r0_km, k1, nd);
+        rhs_dual(kind, fatigue, N, d_const(t, nd), x, u, p, win, tauc, r0_km, k1, nd, fc);
         if (scheme == 1) {
             for (int j = 0; j < nx; ++j) x[j] = d_add(x[j], d_scale(k1[j], h, nd), nd);
         } else if (scheme == 2) {
             for (int j = 0; j < nx; ++j) xs[j] = d_add(x[j], d_scale(k1[j], h / 2, nd), nd);
-            rhs_dual(kind, fatigue, N, d_const(t + h / 2, nd), xs, u, p, win, tauc, r0_km, k2, nd);
+            rhs_dual(kind, fatigue, N, d_const(t + h / 2, nd), xs, u, p, win, tauc, r0_km, k2, nd, fc);
             for (int j = 0; j < nx; ++j) x[j] = d_add(x[j], d_scale(k2[j], h, nd), nd);
         } else {
             for (int j = 0; j < nx; ++j) xs[j] = d_add(x[j], d_scale(k1[j], h / 2, nd), nd);
-            rhs_dual(kind, fatigue, N, d_const(t + h / 2, nd), xs, u, p, win, tauc, r0_km, k2, nd);
+            rhs_dual(kind, fatigue, N, d_const(t + h / 2, nd), xs, u, p, win, tauc, r0_km, k2, nd, fc);
             for (int j = 0; j < nx; ++j) xs[j] = d_add(x[j], d_scale(k2[j], h / 2, nd), nd);
-            rhs_dual(kind, fatigue, N, d_const(t + h / 2, nd), xs, u, p, win, tauc, r0_km, k3, nd);
+            rhs_dual(kind, fatigue, N, d_const(t + h / 2, nd), xs, u, p, win, tauc, r0_km, k3, nd, fc);
             for (int j = 0; j < nx; ++j) xs[j] = d_add(x[j], d_scale(k3[j], h, nd), nd);
-            rhs_dual(kind, fatigue, N, d_const(t + h, nd), xs, u, p, win, tauc, r0_km, k4, nd);
+            rhs_dual(kind, fatigue, N, d_const(t + h, nd), xs, u, p, win, tauc, r0_km, k4, nd, fc);
             for (int j = 0; j < nx; ++j) {
                 dual sum = d_add(d_add(k1[j], d_scale(k2[j], 2.0, nd), nd), d_add(d_scale(k3[j], 2.0, nd), k4[j], nd), nd);
                 x[j] = d_add(x[j], d_scale(sum, h / 6, nd), nd);
@@ -240,7 +242,7 @@ int fes_oracle_ivp(int kind, int fatigue, int scheme, int N, int ns, int S, doub
                 for (int i = 0; i < N; ++i) wd[i] = d_const(w[(size_t)n * N + i], nd);
                 for (int i = 0; i < nu; ++i) ud[i] = d_const(uu[(size_t)n * nu + i], nd);
                 double t0 = dt * n;
-                interval_dual(kind, fatigue, scheme, N, S, t0, (t0 + dt) - t0, x, ud, pd, wd, tauc, r0_km, nd);
+                interval_dual(kind, fatigue, scheme, N, S, t0, (t0 + dt) - t0, x, ud, pd, wd, tauc, r0_km, nd, NULL);
                 if (tr && trace_every != 1) for (int j = 0; j < nx; ++j) tr[(size_t)(n + 1) * nx + j] = x[j].v;
                 if (st) for (int j = 0; j < nx; ++j) for (int k = 0; k < nd; ++k)
                     st[((size_t)(n + 1) * nx + j) * nd + k] = x[j].d[k];
@@ -263,14 +265,15 @@ int fes_oracle_ivp(int kind, int fatigue, int scheme, int N, int ns, int S, doub
  *   Jp [B][ns][nx][n_pdir]    dPhi_k/dparams[pdir] (NULL to skip)
  *   Jw [B][ns][nx][N]         dPhi_k/dwin_k (pulse-time sensitivities; NULL to skip)
  */
-int fes_oracle_shoot(int kind, int fatigue, int scheme, int N, int ns, int S, double dt, double t_start, double tauc,
-                     double r0_km, long long B, const double *params, int params_shared, const double *X,
-                     const double *win, int win_shared, const double *U, int u_shared, int nu,
-                     int n_pdir, const int *pdir, double *G, double *Jx, double *Ju, double *Jp, double *Jw, int n_threads)
+static int shoot_core(int kind, int fatigue, int scheme, int N, int ns, int S, double dt, double t_start, double tauc,
+                      double r0_km, long long B, const double *params, int params_shared, const double *X,
+                      const double *win, int win_shared, const double *U, int u_shared, int nu,
+                      int n_pdir, const int *pdir, double *G, double *Jx, double *Ju, double *Jp, double *Jw, int n_threads,
+                      const double *Fc, int fc_shared, double *Jc)
 {
     int nx = fatigue ? 5 : 2;
-    int ndx = Jx ? nx : 0, ndu = Ju ? nu : 0, ndp = Jp ? n_pdir : 0, ndw = Jw ? N : 0;
-    int nd = ndx + ndu + ndp + ndw;
+    int ndx = Jx ? nx : 0, ndu = Ju ? nu : 0, ndp = Jp ? n_pdir : 0, ndw = Jw ? N : 0, ndc = (Fc && Jc) ? 1 : 0;
+    int nd = ndx + ndu + ndp + ndw + ndc;
     if (N > MAXN || nd > MAXD || (kind == HMED2018 && nu != N) || (kind == DING2007 && nu != 1)) return -1;
 #ifdef _OPENMP
     if (n_threads > 0) omp_set_num_threads(n_threads);
@@ -289,7 +292,12 @@ int fes_oracle_shoot(int kind, int fatigue, int scheme, int N, int ns, int S, do
         for (int i = 0; i < nu; ++i) { ud[i] = d_const(uu[i], nd); if (ndu) ud[i].d[ndx + i] = 1.0; }
         for (int j = 0; j < ndp; ++j) pd[pdir[j]].d[ndx + ndu + j] = 1.0;
         for (int i = 0; i < N; ++i) { wd[i] = d_const(w[i], nd); if (ndw) wd[i].d[ndx + ndu + ndp + i] = 1.0; }
-        interval_dual(kind, fatigue, scheme, N, S, t_start + dt * k, dt, x, ud, pd, wd, tauc, r0_km, nd);
+        dual fcd;
+        if (Fc) {
+            fcd = d_const(Fc[(fc_shared ? 0 : (size_t)b * ns) + k], nd);
+            if (ndc) fcd.d[ndx + ndu + ndp + ndw] = 1.0;
+        }
+        interval_dual(kind, fatigue, scheme, N, S, t_start + dt * k, dt, x, ud, pd, wd, tauc, r0_km, nd, Fc ? &fcd : NULL);
         for (int j = 0; j < nx; ++j) {
             size_t o = ((size_t)b * ns + k) * nx + j;
             G[o] = xk[nx + j] - x[j].v;
@@ -297,9 +305,33 @@ int fes_oracle_shoot(int kind, int fatigue, int scheme, int N, int ns, int S, do
             for (int c = 0; c < ndu; ++c) Ju[o * nu + c] = x[j].d[ndx + c];
             for (int c = 0; c < ndp; ++c) Jp[o * n_pdir + c] = x[j].d[ndx + ndu + c];
             for (int c = 0; c < ndw; ++c) Jw[o * N + c] = x[j].d[ndx + ndu + ndp + c];
+            if (ndc) Jc[o] = x[j].d[ndx + ndu + ndp + ndw];
         }
     }
     return 0;
+}
+
+int fes_oracle_shoot(int kind, int fatigue, int scheme, int N, int ns, int S, double dt, double t_start, double tauc,
+                     double r0_km, long long B, const double *params, int params_shared, const double *X,
+                     const double *win, int win_shared, const double *U, int u_shared, int nu,
+                     int n_pdir, const int *pdir, double *G, double *Jx, double *Ju, double *Jp, double *Jw, int n_threads)
+{
+    return shoot_core(kind, fatigue, scheme, N, ns, S, dt, t_start, tauc, r0_km, B, params, params_shared, X, win, win_shared,
+                      U, u_shared, nu, n_pdir, pdir, G, Jx, Ju, Jp, Jw, n_threads, NULL, 0, NULL);
+}
+
+/* The same with the force factor of f_dot_fun (ding2003.py:309-311: F' = (...) * (fl*fv + fp)) given per interval:
+ *   Fc [B or 1][ns]   c_k = fl*fv + fp held constant over interval k
+ *   Jc [B][ns][nx]    dPhi_k/dc_k (NULL to skip) */
+int fes_oracle_shoot_fc(int kind, int fatigue, int scheme, int N, int ns, int S, double dt, double t_start, double tauc,
+                        double r0_km, long long B, const double *params, int params_shared, const double *X,
+                        const double *win, int win_shared, const double *U, int u_shared, int nu,
+                        int n_pdir, const int *pdir, double *G, double *Jx, double *Ju, double *Jp, double *Jw, int n_threads,
+                        const double *Fc, int fc_shared, double *Jc)
+{
+    if (Fc == NULL) return -1;
+    return shoot_core(kind, fatigue, scheme, N, ns, S, dt, t_start, tauc, r0_km, B, params, params_shared, X, win, win_shared,
+                      U, u_shared, nu, n_pdir, pdir, G, Jx, Ju, Jp, Jw, n_threads, Fc, fc_shared, Jc);
 }
 
 int fes_oracle_max_threads(void)

@@ -176,12 +176,13 @@ def cn_sum(r0, t, win, lam, tauc):
     return total
 
 
-def f_dot(cn, f, a, tau1, km, tau2):
-    """ding2003.py:309 with fl = fv = 1, fp = 0."""
-    return a * (cn / (km + cn)) - (f / (tau1 + tau2 * (cn / (km + cn))))
+def f_dot(cn, f, a, tau1, km, tau2, force_factor=None):
+    """ding2003.py:309-311; force_factor = force_length * force_velocity + passive_force (None: the defaults 1 * 1 + 0)."""
+    fd = a * (cn / (km + cn)) - (f / (tau1 + tau2 * (cn / (km + cn))))
+    return fd if force_factor is None else fd * force_factor
 
 
-def rhs(kind, fatigue, t, x, u, p, win, tauc, r0_km=R0_KM_RELATIONSHIP):
+def rhs(kind, fatigue, t, x, u, p, win, tauc, r0_km=R0_KM_RELATIONSHIP, force_factor=None):
     """dx/dt for one of the six models.
 
     x : [nx, ...]   states Cn, F(, A, Tau1, Km)
@@ -206,7 +207,7 @@ def rhs(kind, fatigue, t, x, u, p, win, tauc, r0_km=R0_KM_RELATIONSHIP):
         a_eff = a * (1 - np.exp(-(u[0] - p[P_PD0]) / p[P_PDT]))  # ding2007.py:188
     else:
         a_eff = a
-    fd = f_dot(cn, f, a_eff, tau1, km, p[P_TAU2])
+    fd = f_dot(cn, f, a_eff, tau1, km, p[P_TAU2], force_factor)
     if not fatigue:
         return np.stack(np.broadcast_arrays(cn_dot, fd))
     a_dot = -(a - p[P_A_REST]) / p[P_TAU_FAT] + p[P_ALPHA_A] * f
@@ -216,10 +217,10 @@ def rhs(kind, fatigue, t, x, u, p, win, tauc, r0_km=R0_KM_RELATIONSHIP):
 
 
 # ---- bioptim's fixed-step integrators over one shooting interval --------------------------------
-def integrate_interval(kind, fatigue, scheme, n_steps, t0, dt, x0, u, p, win, tauc, r0_km=R0_KM_RELATIONSHIP):
+def integrate_interval(kind, fatigue, scheme, n_steps, t0, dt, x0, u, p, win, tauc, r0_km=R0_KM_RELATIONSHIP, force_factor=None):
     """integrator.py:300-365.  Returns xall [nx, n_steps+1, ...] (xall[:, 0] = x0)."""
     h = dt / n_steps
-    fun = lambda tt, xx: rhs(kind, fatigue, tt, xx, u, p, win, tauc, r0_km)
+    fun = lambda tt, xx: rhs(kind, fatigue, tt, xx, u, p, win, tauc, r0_km, force_factor)
     xs = [x0]
     x = x0
     for i in range(1, n_steps + 1):
@@ -263,17 +264,19 @@ def ivp(kind, fatigue, scheme, n_steps, dt, x0, u, p, win, tauc, r0_km=R0_KM_REL
     return np.concatenate(out, axis=1)
 
 
-def shoot(kind, fatigue, scheme, n_steps, dt, X, U, p, win, tauc, r0_km=R0_KM_RELATIONSHIP, t_start=0.0):
+def shoot(kind, fatigue, scheme, n_steps, dt, X, U, p, win, tauc, r0_km=R0_KM_RELATIONSHIP, t_start=0.0, force_factor=None):
     """Multiple-shooting end points and defects (penalty.py:1092-1099).
 
     X [ns+1, nx, ...]; U None | [ns, nu, ...]; win [ns(+1), N, ...]
     Returns (phi [ns, nx, ...], g [ns, nx, ...]) with g_k = x_{k+1} - Phi_k(x_k, u_k, p).
+    force_factor None | [ns, ...]: fl * fv + fp of the interval (ding2003.py:309-311), held constant over it.
     """
     ns = X.shape[0] - 1
     phi = []
     for k in range(ns):
         un = None if U is None else U[k]
-        xall = integrate_interval(kind, fatigue, scheme, n_steps, t_start + dt * k, dt, X[k], un, p, win[k], tauc, r0_km)
+        fc = None if force_factor is None else force_factor[k]
+        xall = integrate_interval(kind, fatigue, scheme, n_steps, t_start + dt * k, dt, X[k], un, p, win[k], tauc, r0_km, fc)
         phi.append(xall[:, -1])
     phi = np.stack(phi)
     return phi, X[1:] - phi

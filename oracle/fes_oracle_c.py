@@ -27,6 +27,7 @@ def build(force: bool = False) -> Path:
 def _bind(cdll):
     cdll.fes_oracle_ivp.restype = ctypes.c_int
     cdll.fes_oracle_shoot.restype = ctypes.c_int
+    cdll.fes_oracle_shoot_fc.restype = ctypes.c_int
     cdll.fes_oracle_max_threads.restype = ctypes.c_int
     return cdll
 
@@ -110,8 +111,9 @@ def ivp(kind, fatigue, scheme, N, ns, S, dt, tauc, r0_km, params, x0, win, u=Non
 
 
 def shoot(kind, fatigue, scheme, N, ns, S, dt, t_start, tauc, r0_km, params, X, win, U=None, pdir=(),
-          want_x=True, want_u=False, want_w=False, n_threads=0):
-    """X [B, ns+1, nx]; win [B|1, ns+1, N]; U [B|1, ns, nu] -> dict(G, Jx, Ju, Jp, Jw)."""
+          want_x=True, want_u=False, want_w=False, n_threads=0, force_factor=None):
+    """X [B, ns+1, nx]; win [B|1, ns+1, N]; U [B|1, ns, nu] -> dict(G, Jx, Ju, Jp, Jw[, Jc]).
+    force_factor [B|1, ns]: fl*fv + fp of f_dot_fun (ding2003.py:309-311) per interval; adds Jc [B, ns, nx]."""
     nx = 5 if fatigue else 2
     X = _c(X).reshape(-1, ns + 1, nx)
     B = X.shape[0]
@@ -128,13 +130,20 @@ def shoot(kind, fatigue, scheme, N, ns, S, dt, t_start, tauc, r0_km, params, X, 
     Ju = np.empty((B, ns, nx, nu)) if (want_u and nu) else None
     Jp = np.empty((B, ns, nx, len(pdir_a))) if len(pdir_a) else None
     Jw = np.empty((B, ns, nx, N)) if want_w else None
-    rc = lib().fes_oracle_shoot(
+    args = [
         ctypes.c_int(kind), ctypes.c_int(int(fatigue)), ctypes.c_int(scheme), ctypes.c_int(N), ctypes.c_int(ns),
         ctypes.c_int(S), ctypes.c_double(dt), ctypes.c_double(t_start), ctypes.c_double(tauc),
         ctypes.c_double(r0_km), ctypes.c_longlong(B), _p(params), ctypes.c_int(int(params.shape[0] == 1)),
         _p(X), _p(win), ctypes.c_int(int(win.shape[0] == 1)), _p(U),
         ctypes.c_int(int(U is not None and U.shape[0] == 1)), ctypes.c_int(nu),
-        ctypes.c_int(len(pdir_a)), _p(pdir_a), _p(G), _p(Jx), _p(Ju), _p(Jp), _p(Jw), ctypes.c_int(n_threads))
+        ctypes.c_int(len(pdir_a)), _p(pdir_a), _p(G), _p(Jx), _p(Ju), _p(Jp), _p(Jw), ctypes.c_int(n_threads)]
+    out = {"G": G, "Jx": Jx, "Ju": Ju, "Jp": Jp, "Jw": Jw}
+    if force_factor is None:
+        rc = lib().fes_oracle_shoot(*args)
+    else:
+        fc = _c(force_factor).reshape(-1, ns)
+        out["Jc"] = np.empty((B, ns, nx))
+        rc = lib().fes_oracle_shoot_fc(*args, _p(fc), ctypes.c_int(int(fc.shape[0] == 1)), _p(out["Jc"]))
     if rc != 0:
         raise RuntimeError(f"fes_oracle_shoot rc={rc}")
-    return {"G": G, "Jx": Jx, "Ju": Ju, "Jp": Jp, "Jw": Jw}
+    return out

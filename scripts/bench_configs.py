@@ -46,7 +46,7 @@ def kernel_name(entry, dtype, kind, fatigue=None, groups=None):
     t = "double" if dtype in ("f64", torch.float64) else "float"
     if entry == "ident":   # shared stimulation train and controls: the variant that stages them in shared memory
         return f"fes_ident_kernel<{t}, {KIND_NAME[kind]}, staged>"
-    bits = ((1, "X0"), (2, "U"), (4, "P"), (16, "PF"), (8, "W"))
+    bits = ((1, "X0"), (2, "U"), (32, "C"), (4, "P"), (16, "PF"), (8, "W"))
     g = "|".join(n for b, n in bits if groups & b) or "0"
     return f"fes_{entry}_kernel<{t}, {KIND_NAME[kind]}, {'fatigue' if fatigue else 'no_fatigue'}, {g}>"
 
@@ -250,7 +250,7 @@ def run_configs(wanted, dev, dtype="f64", steps=3, warmup=3, scale=1.0, flush=No
                  "best_cost": float(out.cost[out.best()].item())})
         del p, x0
 
-    if {"5", "5pf"} & set(wanted):
+    if {"5", "5pf", "5c"} & set(wanted):
         B = max(1024, int((1 << 16) * scale))
         proto, p, X, U = protocols.nmpc_scenarios(B, device=dev)
         p, X, U = p.to(dt_t), X.to(dt_t), U.to(dt_t)
@@ -270,6 +270,17 @@ def run_configs(wanted, dev, dtype="f64", steps=3, warmup=3, scale=1.0, flush=No
                 kernel_name("shoot", dtype, fes.FES_DING2007, True, fes.FES_DIR_X0 | fes.FES_DIR_U), B * ns * S, ms, ob,
                 (X.numel() + U.numel()) * esz, dtype, {"scenarios": B, "n_shooting": ns, "interval_integrations": B * ns,
                                                        "one_shot_shoot_call_ms": statistics.mean(ms1)})
+        if "5c" in wanted:
+            # the same horizon with the force factor fl * fv + fp of every interval as an input (the FES-MSK seam) and d Phi / d factor
+            g = torch.Generator(device="cpu").manual_seed(6)
+            fc = torch.empty((ns, B), dtype=torch.float64).uniform_(0.5, 1.2, generator=g).to(dev).to(dt_t)
+            ext = torch.cat([U[:ns], fc[:, None, :]], dim=1).contiguous()
+            plan_c = fes.ShootPlan(fes.FES_DING2007, True, p, win, proto["dt"], ns, B, n_steps=S, ctrl=ext, dtype=dt_t, force_factor=True)
+            out, ms = timed(lambda: plan_c(X, ext), steps, warmup, flush)
+            ob = (out.G.numel() + out.Jx.numel() + out.Ju.numel() + out.Jc.numel()) * esz
+            add("5c: the same horizon with the force factor fl*fv + fp per interval as an input, + dPhi/dfactor (ShootPlan call)",
+                kernel_name("shoot", dtype, fes.FES_DING2007, True, fes.FES_DIR_X0 | fes.FES_DIR_U | fes.FES_DIR_C), B * ns * S, ms, ob,
+                (X.numel() + ext.numel()) * esz, dtype, {"scenarios": B, "n_shooting": ns})
         if "5pf" in wanted:
             # the dense parameter columns of a fatigue model (what a fatigue-parameter identification would differentiate)
             fn = lambda: fes.shoot(fes.FES_DING2007, True, p, X, win, proto["dt"], n_steps=S, ctrl=U, want=("p", "pf"),

@@ -41,8 +41,8 @@ for stage in "$@"; do
           python -c "import sys, json; d = json.loads(sys.stdin.read()); print(json.dumps({'batch': d['config']['batch_per_gpu'], 'value': d['value'], 'ms': d['ms_per_step'], 'pipe': d['roofline']['pipe']['frac_of_nominal'] if d['roofline']['pipe'] else None}))" | tee -a gpurun_out/strong1_$tag.jsonl
       done ;;
     configs)
-      timeout 900 python scripts/bench_configs.py --configs 1,2fwd,3,4,4b,4c,5,5pf > gpurun_out/configs_f64_$tag.jsonl 2> gpurun_out/configs_f64_$tag.err; echo "rc=$?"
-      timeout 900 python scripts/bench_configs.py --configs 1,2fwd,2x0,3,4,4b,4c,5,5pf --dtype f32 > gpurun_out/configs_f32_$tag.jsonl 2> gpurun_out/configs_f32_$tag.err; echo "rc=$?"
+      timeout 900 python scripts/bench_configs.py --configs 1,2fwd,3,4,4b,4c,5,5c,5pf > gpurun_out/configs_f64_$tag.jsonl 2> gpurun_out/configs_f64_$tag.err; echo "rc=$?"
+      timeout 900 python scripts/bench_configs.py --configs 1,2fwd,2x0,3,4,4b,4c,5,5c,5pf --dtype f32 > gpurun_out/configs_f32_$tag.jsonl 2> gpurun_out/configs_f32_$tag.err; echo "rc=$?"
       cut -c1-260 gpurun_out/configs_f64_$tag.jsonl gpurun_out/configs_f32_$tag.jsonl ;;
     margin)
       timeout 900 python scripts/parity_margin.py > gpurun_out/parity_margin_$tag.txt 2>&1; echo "margin rc=$?"; cat gpurun_out/parity_margin_$tag.txt ;;

@@ -33,9 +33,12 @@ def get(name, scale=None):
 
 
 rd, wr = get("dram__bytes_read.sum", "bytes"), get("dram__bytes_write.sum", "bytes")
-sha = json.loads((ROOT / "cocofest_b200" / "csrc" / "sass_counts.json").read_text())["sass_sha256"]
+counts = json.loads((ROOT / "cocofest_b200" / "csrc" / "sass_counts.json").read_text())
+sha = counts["sass_sha256"]
+kernel = f"fes_ivp_kernel<{'double' if dtype == 'f64' else 'float'}, DING2003, fatigue, X0>"
+ksha = counts["kernels"][kernel]["sass_sha256"]   # the device code of the captured kernel alone: what bench.py compares
 d = {
-    "report": f"{rep} (summary: {summary})", "batch": batch, "final_time_s": final_time, "dtype": dtype, "sass_sha256": sha,
+    "report": f"{rep} (summary: {summary})", "batch": batch, "final_time_s": final_time, "dtype": dtype, "sass_sha256": sha, "kernel": kernel, "kernel_sass_sha256": ksha,
     "dram_bytes_read": int(rd), "dram_bytes_write": int(wr), "dram_bytes": int(rd + wr),
     "gpu_time_duration_s": get("gpu__time_duration.sum", "seconds"),
     "fp64_pipe_active_pct": get("sm__pipe_fp64_cycles_active.avg.pct_of_peak_sustained_active"),

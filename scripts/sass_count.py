@@ -23,7 +23,7 @@ from pathlib import Path
 ROOT = Path(__file__).resolve().parent.parent
 FP = re.compile(r"\b(DFMA|DMUL|DADD|FFMA2|FMUL2|FADD2|FFMA|FMUL|FADD|MUFU\.\w+)\b")
 KIND = {"0": "DING2003", "1": "DING2007", "2": "HMED2018"}
-GROUP_BITS = ((1, "X0"), (2, "U"), (4, "P"), (16, "PF"), (8, "W"))
+GROUP_BITS = ((1, "X0"), (2, "U"), (32, "C"), (4, "P"), (16, "PF"), (8, "W"))
 
 
 def pretty(sym):
@@ -95,6 +95,9 @@ def main():
             "fp32_flop": 2 * mix["FFMA"] + mix["FMUL"] + mix["FADD"] + 2 * (2 * mix["FFMA2"] + mix["FMUL2"] + mix["FADD2"]),
             "mufu": sum(v for k, v in mix.items() if k.startswith("MUFU")),
             "local_loads": ldl, "local_stores": stl,
+            # the device code of THIS kernel alone: what a measurement of the kernel (ncu traffic) is tied to, so that adding
+            # or changing another kernel of the library does not orphan it
+            "sass_sha256": hashlib.sha256(block.encode()).hexdigest(),
         }
         rec.update(usage.get(sym, {}))
         kernels[pretty(sym)] = rec

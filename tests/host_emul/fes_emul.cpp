@@ -160,6 +160,15 @@ int shoot_kf(int groups, const ShootArgs<T> &a) {
         case G_U:
             if constexpr (KIND != DING2003) return shoot_cpu<T, KIND, FAT, G_U>(a);
             else return E_DIRS;
+        case G_X0 | G_U | G_C:
+            if constexpr (KIND != DING2003) return shoot_cpu<T, KIND, FAT, G_X0 | G_U | G_C>(a);
+            else return shoot_cpu<T, KIND, FAT, G_X0 | G_C>(a);
+        case G_X0 | G_C:
+            if constexpr (KIND == DING2003) return shoot_cpu<T, KIND, FAT, G_X0 | G_C>(a);
+            else return E_DIRS;
+        case G_U | G_C:  // Hmed2018: the intensity tiles after the first of a call that carries the force factor
+            if constexpr (KIND == HMED2018) return shoot_cpu<T, KIND, FAT, G_U | G_C>(a);
+            else return E_DIRS;
         case G_P: return shoot_cpu<T, KIND, FAT, G_P>(a);
         case G_P | G_PF:
             if constexpr (FAT) return shoot_cpu<T, KIND, FAT, G_P | G_PF>(a);
@@ -203,7 +212,7 @@ int shoot_impl(const FesDesc *d, const FesShootBuffers *b) {
     int rc = check_desc(d, false);
     if (rc) return rc;
     if (!b || !b->params || !b->X) return E_BUF;
-    if (num_controls(d->model_kind, d->n_trunc) > 0 && !b->ctrl) return E_BUF;
+    if (num_controls(d->model_kind, d->n_trunc) + ((d->dirs & FES_DIR_C) ? 1 : 0) > 0 && !b->ctrl) return E_BUF;
     int groups = d->dirs;
     if (d->model_kind == FES_DING2003) groups &= ~FES_DIR_U;
     const int nd = num_dirs(d->model_kind, d->fatigue, groups);
