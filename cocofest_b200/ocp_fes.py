@@ -60,23 +60,25 @@ class FesShooting:
     def _params(self, params):
         return torch.as_tensor(self.model.param_vector() if params is None else params).to(self.device)
 
-    def evaluate(self, X, U=None, params=None, want=("x", "u"), defects=True, endpoints=False) -> _fes.ShootResult:
-        """X [ns+1, nx, B]; U [ns, nu(, B)]; params None | [14(, B)].  Returns fes.ShootResult."""
+    def evaluate(self, X, U=None, params=None, want=("x", "u"), defects=True, endpoints=False, force_factor=None) -> _fes.ShootResult:
+        """X [ns+1, nx, B]; U [ns, nu(, B)]; params None | [14(, B)].  Returns fes.ShootResult.
+        force_factor [ns(, B)]: ``fl * fv + fp`` of every interval (FES-MSK coupling, see ``fes.shoot``); adds ``Jc``."""
         return _fes.shoot(self.model.kind, self.model.with_fatigue, self._params(params),
                           torch.as_tensor(X).to(self.device), self.window, self.dt, n_steps=self.n_steps,
                           ctrl=None if U is None else torch.as_tensor(U).to(self.device), scheme=self.scheme,
                           want=want, t_start=self.t_start, tauc=self.model.tauc, r0_km=self.model.r0_km_relationship,
-                          defects=defects, endpoints=endpoints, dtype=self.dtype)
+                          defects=defects, endpoints=endpoints, dtype=self.dtype,
+                          force_factor=None if force_factor is None else torch.as_tensor(force_factor).to(self.device))
 
-    def plan(self, batch, U=None, params=None, want=("x", "u"), defects=True, endpoints=False) -> _fes.ShootPlan:
+    def plan(self, batch, U=None, params=None, want=("x", "u"), defects=True, endpoints=False, force_factor=False) -> _fes.ShootPlan:
         """The same evaluation set up once for a solver loop (``fes.ShootPlan``): ``p = shooting.plan(B, U0); res = p(X, U)``
         per iteration.  ``U`` / ``params`` are templates of the shapes the calls will use; the plan's result tensors are
-        reused from call to call."""
+        reused from call to call.  force_factor=True: ``U`` is [ns, nu + 1, B], the force factor in its last row."""
         return _fes.ShootPlan(self.model.kind, self.model.with_fatigue, self._params(params), self.window, self.dt,
                               self.n_shooting, batch, n_steps=self.n_steps,
                               ctrl=None if U is None else torch.as_tensor(U).to(self.device), scheme=self.scheme, want=want,
                               t_start=self.t_start, tauc=self.model.tauc, r0_km=self.model.r0_km_relationship,
-                              defects=defects, endpoints=endpoints, dtype=self.dtype)
+                              defects=defects, endpoints=endpoints, dtype=self.dtype, force_factor=force_factor)
 
     # ---- second derivatives (for an exact-Hessian solver) ---------------------------------------------
     # typical magnitudes of (Cn, F, A, Tau1, Km) and of the controls: floors of the finite-difference steps

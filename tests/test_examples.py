@@ -47,3 +47,10 @@ def test_truncation_sweep_example_runs(tmp_path):
     r = _run("sensitivity", "truncation_sweep.py", args=("--max-stim", "15", "--modes", "single,triplet", "--out-dir", str(tmp_path)))
     assert r.returncode == 0, r.stderr[-2000:]
     assert "total: 240 points" in r.stdout and (tmp_path / "truncation_triplet.pkl").exists()
+
+
+@pytest.mark.gpu
+def test_force_factor_example_runs():
+    r = _run("dynamics", "force_length_velocity_factor.py", args=("--scenarios", "4096"))
+    assert r.returncode == 0, r.stderr[-2000:]
+    assert "with    relationships" in r.stdout and "through Jc" in r.stdout
