@@ -129,3 +129,23 @@ def test_identify_stays_inside_its_buffers(monkeypatch, shared_ctrl, max_iter):
     arena.check()
     assert all(same(a, b) for a, b in ((got.params, plain.params), (got.cost, plain.cost), (got.grad, plain.grad),
                                        (got.hess, plain.hess), (got.evaluations, plain.evaluations)))
+
+
+@pytest.mark.parametrize("name", ["ding2003_with_fatigue", "ding2007", "hmed2018_with_fatigue"])
+def test_shoot_with_force_factor_stays_inside_its_buffers(monkeypatch, name):
+    """The extended control rows (model controls + force factor) and the extra Jacobian column, all three kernel sets
+    (X0|C, X0|U|C, U|C for the later intensity tiles)."""
+    dev = torch.device("cuda", 0)
+    pb = random_problem(name, seed=2, B=70, N=12, ns=9, shared_ctrl=False)
+    params, x0, win, ctrl = to_lib(pb, dev)
+    X = (x0[None] * torch.ones((pb["ns"] + 1, 1, 1), dtype=torch.float64, device=dev)).contiguous()
+    fc = torch.linspace(0.6, 1.2, pb["ns"] * pb["B"], dtype=torch.float64, device=dev).reshape(pb["ns"], pb["B"]).contiguous()
+    call = lambda p, x, w, c, f: fes.shoot(pb["kind"], pb["fat"], p, x, w, pb["dt"], n_steps=4, ctrl=c, endpoints=True, force_factor=f)
+    plain = call(params, X, win, ctrl, fc)
+    arena = Arena()
+    with monkeypatch.context() as mp:
+        mp.setattr(fes, "_empty", arena)
+        got = call(padded(params), padded(X), padded(win), padded(ctrl), padded(fc))
+        torch.cuda.synchronize()
+    arena.check()
+    assert all(same(a, b) for a, b in ((got.G, plain.G), (got.Phi, plain.Phi), (got.Jx, plain.Jx), (got.Ju, plain.Ju), (got.Jc, plain.Jc)))

@@ -58,6 +58,25 @@ def test_shoot_on_host_tensors_runs_every_pass_on_the_device():
     assert fes.last_host_timing()["kernels_ms"] > 0
 
 
+def test_shoot_with_force_factor_on_host_tensors():
+    """One pass (Ding2007) goes through fes_shoot_host_* with the extended control rows; three passes (Hmed2018, N = 12) are
+    staged on the device once."""
+    dev = torch.device("cuda", 0)
+    for name, passes in (("ding2007_with_fatigue", 1), ("hmed2018_with_fatigue", 3)):
+        pb = random_problem(name, B=200, N=12, ns=5, seed=8, shared_ctrl=False)
+        params, x0, win, ctrl = to_lib(pb, dev)
+        rng = np.random.default_rng(2)
+        X = (x0[None] * torch.tensor(rng.uniform(0.9, 1.1, (pb["ns"] + 1, pb["nx"], pb["B"])), device=dev)).contiguous()
+        fc = torch.tensor(rng.uniform(0.5, 1.2, (pb["ns"], pb["B"])), device=dev)
+        d = fes.shoot(pb["kind"], pb["fat"], params, X, win, pb["dt"], n_steps=5, ctrl=ctrl, endpoints=True, force_factor=fc)
+        n0 = _lib.lib().fes_launch_count()
+        hp, hX, hw, hc, hf = _cpu(params, X, win, ctrl, fc)
+        h = fes.shoot(pb["kind"], pb["fat"], hp, hX, hw, pb["dt"], n_steps=5, ctrl=hc, endpoints=True, force_factor=hf)
+        assert _lib.lib().fes_launch_count() - n0 == passes + 1
+        for a, b in ((h.G, d.G), (h.Phi, d.Phi), (h.Jx, d.Jx), (h.Ju, d.Ju), (h.Jc, d.Jc)):
+            assert a.device.type == "cpu" and torch.equal(a, b.cpu())
+
+
 def test_identify_host_equals_device():
     dev = torch.device("cuda", 0)
     from cocofest_b200 import protocols
