@@ -72,7 +72,7 @@ for l in sys.stdin:
       echo "ncu_list rc=$?"; tail -3 gpurun_out/launches_bench_$tag.csv ;;
     ncu_full:*)
       cfg=${stage#ncu_full:}; dt=f64; case $cfg in *@f32) dt=f32; cfg=${cfg%@f32};; esac
-      pat=fes_ivp_kernel; case $cfg in 4b|4c) pat=fes_ident_kernel;; 5|5pf) pat=fes_shoot_kernel;; esac
+      pat=fes_ivp_kernel; case $cfg in 4b|4c) pat=fes_ident_kernel;; 5|5c|5pf) pat=fes_shoot_kernel;; esac
       cmd="python scripts/bench_configs.py --configs $cfg --dtype $dt --steps 1 --warmup 1 --t2 ${T2:-300}"
       timeout 600 $cmd > gpurun_out/ncu_full_plain_${cfg}_${dt}_$tag.log 2>&1 &&
       timeout 1500 ncu --set full --clock-control none --import-source on -k regex:$pat -s 1 -c 1 -f -o gpurun_out/prof_${cfg}_${dt}_$tag $cmd > gpurun_out/ncu_full_${cfg}_${dt}_$tag.log 2>&1
