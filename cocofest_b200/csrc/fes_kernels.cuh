@@ -175,6 +175,8 @@ __global__ void FES_LAUNCH_BOUNDS fes_ivp_kernel(const IvpArgs<T> a) {
     auto put_state = [&](int64_t pt) {
         if (a.trace != nullptr) {
 #pragma unroll
+            // plain stores: streaming stores (__stcs) made the write-bound config 1 SLOWER, 0.947 against 0.908 ms
+            // (profiles/r02_tune_trace_stcs_af.txt)
             for (int j = 0; j < NX; ++j) a.trace[(pt * NX + j) * a.trace_B + b] = x[j];
         }
     };

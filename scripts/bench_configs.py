@@ -172,10 +172,17 @@ def run_configs(wanted, dev, dtype="f64", steps=3, warmup=3, scale=1.0, flush=No
         # IvpPlan = the built problem (what IvpFes(...) is to the reference); the timed call is one integrate()
         fn = fes.IvpPlan(fes.FES_DING2003, True, p, x0, win, 1.0 / ns, n_steps=S, n_shooting=ns, trace="steps", dtype=dt_t)
         out, ms = timed(fn, steps, warmup, flush)
+        # this configuration is a pure WRITE stream; MEASURED_PEAKS.json's figure is a copy (reads + writes): measure what
+        # a plain fill of a buffer of the same size reaches on this device, as the denominator that applies
+        probe = torch.empty_like(out.trace)
+        _, ms_fill = timed(lambda: probe.fill_(1.0), steps, warmup, flush)
+        fill_gbs = probe.numel() * esz / (statistics.mean(ms_fill) * 1e-3) / 1e9
+        del probe
         add("1: README IvpFes DingModelFrequencyWithFatigue x B, all 101 points x 5 states written",
             kernel_name("ivp", dtype, fes.FES_DING2003, True, 0), B * ns * S, ms,
             out.trace.numel() * esz + out.x_final.numel() * esz, x0.numel() * esz, dtype,
-            {"batch": B, "n_shooting": ns, "F_end": float(out.x_final[1, 0])})
+            {"batch": B, "n_shooting": ns, "F_end": float(out.x_final[1, 0]),
+             "write_stream": {"fill_of_the_same_size_gbs": fill_gbs, "what": "torch fill_ of a buffer as large as the trace: the write-only rate of this device"}})
         del out, x0
 
     for tag, dirs in (("2fwd", 0), ("2x0", fes.FES_DIR_X0), ("2pf", fes.FES_DIR_P | fes.FES_DIR_PF)):
