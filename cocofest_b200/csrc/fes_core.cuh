@@ -529,6 +529,9 @@ struct Tangent {
     // state) sit a few bits above a float's resolution of the state, so a float accumulator loses ~3e-4 of every increment:
     // measured 9e-5 relative drift of A after 20 s of the fatigue protocol, growing linearly.  The increments themselves are
     // formed in float; only the three running sums (3 DADD per step on the otherwise idle fp64 pipe) are double.
+    // (Pairs of floats with TwoSum instead -- no F64 <-> F32 conversions, 9 fewer XU-pipe instructions but 30 more FP32
+    // ones per step -- were built and measured: 1064.8 against 1045.0 ms, profiles/r02_tune_f32_float_pair_acc_ak.json.  The
+    // float kernel is bound by its FP32 issue slots; conversions on the XU pipe are close to free.)
     double xd[3];
 
     // x = the state the integration starts from (seeds the double accumulators of the f32 build)

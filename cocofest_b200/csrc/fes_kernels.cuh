@@ -33,7 +33,7 @@ constexpr int BLOCK = FES_BLOCK;
 // RK4 steps fused into one basic block (rk4_steps in fes_core.cuh): how many, per kernel family, by measurement on the B200
 // (profiles/r02_tune_step_unroll_{r,s}.txt; u2 / u5 / u10 = blocks of 2 / 5 / 10 steps, S = 10):
 //   trajectory kernel  fp64 headline +2.0 % (u2), +1.7 % (u5), +0.8 % (u10); config 3 +2.2 %; dense P|PF columns +4.0 % (u2);
-//                      fp32 headline +7.7 % (u2), config 3 +10.7 % (u2)                                         -> pairs
+//                      fp32 headline +7.7 % (u2), +9.7 % (u5); fp32 config 3 +10.7 % (u2), +7.7 % (u5)   -> pairs (fp32 x0: five)
 //   interval kernel    fp64 config 5 (X0|U): 0.484 (u1), 0.486 (u2), 0.469 (u5), 0.571 ms (u10); config 5pf (dense P|PF): 0.790 (u1),
 //                      0.758 (u2), 0.804 ms (u5); fp32 config 5: 0.341 (u1), 0.342 (u2), 0.352 ms (u5)  -> 5 / pairs / single (fp32)
 //   identification     10.56 (u1), 10.75 (u2), 11.48 (u5), 12.03 ms (u10): it already spills its Lambda cache under the cap -> single
@@ -43,6 +43,16 @@ constexpr int BLOCK = FES_BLOCK;
 #ifndef FES_IDENT_UNROLL
 #define FES_IDENT_UNROLL 1
 #endif
+template <typename T, bool FAT, int GROUPS>
+constexpr int ivp_unroll() {
+#ifdef FES_IVP_UNROLL_ALL
+    return FES_IVP_UNROLL_ALL;
+#else
+    // the fp32 fatigue kernel with the x0 columns is the one trajectory kernel that gains from blocks of five
+    // (209.0 against 212.9 ms with pairs, 229.3 ms with single steps; config 3 in fp32 prefers pairs)
+    return (sizeof(T) == 4 && FAT && GROUPS == G_X0) ? 5 : FES_IVP_UNROLL;
+#endif
+}
 template <typename T, bool FAT, int GROUPS>
 constexpr int shoot_unroll() {
 #ifdef FES_SHOOT_UNROLL
@@ -221,7 +231,7 @@ __global__ void FES_LAUNCH_BOUNDS fes_ivp_kernel(const IvpArgs<T> a) {
             Interval<T, ND> iv;
             interval_setup<T, KIND, FAT, GROUPS>(
                 tr, [&](int c) { return trow[c * tstr]; }, [&](int c) { return crow[c * cstr]; }, a.N, a.tile_off, iv, lcp);
-            constexpr int UNROLL = FES_IVP_UNROLL;
+            constexpr int UNROLL = ivp_unroll<T, FAT, GROUPS>();
             int i = 0;
             if constexpr (UNROLL > 1)
                 if (a.scheme == 4 && !(tr_on && a.trace_mode == 1))
