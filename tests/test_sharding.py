@@ -53,9 +53,30 @@ def _worker(rank, world, port, out_dir):
         assert torch.equal(sharding.gather_last(mine.x_final), full_x)
         even = sharding.gather_last(mine.sens_final[..., :18].contiguous())
         assert even.shape == (5, 5, 36) and torch.equal(even[..., :18], full_s[..., :18]) and torch.equal(even[..., 18:], full_s[..., 19:])
+        # the other two entry points shard the same way (the batch is the last axis everywhere): scenarios of a
+        # multiple-shooting evaluation with the force factor as an input, candidates of an identification
+        ns = 6
+        winN = win[:ns + 1]
+        X = (x0[None] * torch.linspace(1.0, 0.8, ns + 1, dtype=torch.float64)[:, None, None]).contiguous()
+        fc = (0.6 + 0.5 * torch.rand((ns, B), generator=torch.Generator().manual_seed(1), dtype=torch.float64))
+        shoot = lambda p, x, f: fes.shoot(fes.FES_DING2003, True, p, x, winN, proto["dt"], n_steps=10, force_factor=f)
+        sh = shoot(sharding.shard_last(params, rank, world), sharding.shard_last(X, rank, world), sharding.shard_last(fc, rank, world))
+        G, Jx, Jc = (sharding.gather_last(t.contiguous(), batch=B) for t in (sh.G, sh.Jx, sh.Jc))
+        proto_h, cand, x0_h, ctrl_h = protocols.hmed2018_candidates(B)
+        win_h = torch.tensor(proto_h["win"])
+        truth = torch.tensor(fes.default_params(fes.FES_HMED2018))
+        target = fes.ivp(fes.FES_HMED2018, False, truth, x0_h[:, :1].contiguous(), win_h, proto_h["dt"], ctrl=ctrl_h,
+                         n_shooting=proto_h["ns"], trace="nodes").trace[:, 1, 0].contiguous()
+        ident = lambda p: fes.identify(fes.FES_HMED2018, p, win_h, proto_h["dt"], target, ctrl=ctrl_h, max_iter=2)
+        idm = ident(sharding.shard_last(cand, rank, world))
+        P, C = sharding.gather_last(idm.params, batch=B), sharding.gather_last(idm.cost, batch=B)
         if rank == 0:
             ref = run(params, x0)
             assert torch.equal(full_x, ref.x_final) and torch.equal(full_s, ref.sens_final)
+            rs = shoot(params, X, fc)
+            assert torch.equal(G, rs.G) and torch.equal(Jx, rs.Jx) and torch.equal(Jc, rs.Jc)
+            ri = ident(cand)
+            assert torch.equal(P, ri.params) and torch.equal(C, ri.cost)
             open(os.path.join(out_dir, "ok"), "w").write("ok")
     finally:
         dist.destroy_process_group()
