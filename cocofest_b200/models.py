@@ -19,7 +19,7 @@ from abc import ABC, abstractmethod
 import numpy as np
 
 from . import fes as _fes
-from ._lib import FES_DING2003, FES_DING2007, FES_HMED2018, FES_NP, PARAM_INDEX
+from ._lib import FES_DING2003, FES_DING2007, FES_HMED2018, PARAM_INDEX
 
 
 class FesModel(ABC):

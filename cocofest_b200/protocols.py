@@ -3,11 +3,10 @@
 see the same inputs."""
 from __future__ import annotations
 
-import numpy as np
 import torch
 
 from . import fes
-from ._lib import FES_DING2003, FES_DING2007, FES_HMED2018, FES_NP, PARAM_INDEX
+from ._lib import FES_DING2003, FES_DING2007, FES_HMED2018, PARAM_INDEX
 
 
 def fatigue_protocol(final_time=300, frequency=33, on_s=1, period_s=2, truncation=10):

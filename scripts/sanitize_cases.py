@@ -11,7 +11,6 @@ from pathlib import Path
 ROOT = Path(__file__).resolve().parent.parent
 sys.path.insert(0, str(ROOT))
 
-import numpy as np  # noqa: E402
 import torch  # noqa: E402
 
 from cocofest_b200 import fes, protocols  # noqa: E402
