@@ -17,15 +17,21 @@
  *                  (the Jacobian blocks dPhi/dx_k, dPhi/du_k, dPhi/dp that nlpsol builds in
  *                  external/bioptim/bioptim/interfaces/interface_utils.py:88-95), batched over
  *                  (scenario, interval) pairs.
+ *                  With FES_DIR_C the F row carries the factor fl*fv + fp of f_dot_fun
+ *                  (cocofest/models/ding2003.py:309-311) that the FES-MSK models evaluate from the joint states
+ *                  (cocofest/models/dynamical_model.py:259-310), as an input with its own Jacobian column.
+ *   fes_identify_* replaces the force-tracking objective and the parameter search of the identification OCP
+ *                  (cocofest/optimization/fes_identification_ocp.py:248-299), one candidate per thread.
  *   model arithmetic: cocofest/models/ding2003.py:200-311, ding2003_with_fatigue.py:138-240,
  *                  ding2007.py:121-188, ding2007_with_fatigue.py:133-241, hmed2018.py:119-180,
  *                  hmed2018_with_fatigue.py:124-229.
  *
  * Conventions
  *   - every function returns int: 0 = OK, < 0 = invalid argument (fes_strerror), > 0 = cudaError_t.
- *   - fes_ivp_* / fes_shoot_* take DEVICE pointers owned by the caller; the library allocates nothing
- *     persistent and keeps no global state; calls are re-entrant; work is enqueued on `stream`
- *     (a cudaStream_t passed as void*) and NOT synchronised.
+ *   - fes_ivp_* / fes_shoot_* / fes_identify_* take DEVICE pointers owned by the caller; the library allocates
+ *     nothing persistent and keeps no global state; calls are re-entrant; work is enqueued on `stream`
+ *     (a cudaStream_t passed as void*) and NOT synchronised.  (fes_shoot_static_f64 is the exception: it keeps its
+ *     tables in a static device array shared by all calls on a device, see its declaration.)
  *   - fes_*_host_* take HOST pointers (pinned for full speed), stage through stream-ordered temporary
  *     device allocations from a library-owned pool that stays mapped between calls (fes_host_pool_trim
  *     releases it), and return after the results are in the host buffers.
