@@ -199,6 +199,8 @@ int fes_shoot_f32(const FesDesc *desc, const FesShootBuffers *buf, void *stream)
  *   - returns -8 (see fes_strerror) when fes_workspace_bytes(desc, 0) > FES_STATIC_SCRATCH_BYTES = 4 MiB: a shared
  *     window (FES_WIN_SHARED) needs n_shooting * r + 6 n_steps + 1 doubles, r = 2 + 2 n_trunc for FES_HMED2018 or
  *     FES_DIR_W and 2 otherwise; per-scenario windows need batch times the first term;
+ *   - the first call on a device resolves the array's device address (cudaGetSymbolAddress, once per device): make one
+ *     call before a stream capture begins;
  *   - ALL calls on a device share the array: calls that may overlap on the GPU (different streams, or graphs replayed
  *     concurrently) race on it -- keep them on one stream or order them with events;
  *   - the array keeps the last call's tables; every call rebuilds all it reads before reading it (nothing has to start
