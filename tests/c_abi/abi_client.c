@@ -6,6 +6,8 @@
  *
  *   abi_client            run the case; exit code 0, or 10 + (library return code != 0)
  *   abi_client --errors   exercise the argument checks only (no device work): exit 0 when every bad call is refused
+ *   abi_client --factor   the three intervals of the same case through fes_shoot_host_f64 with the force factor of every
+ *                         interval as an input (FES_DIR_X0 | FES_DIR_C): prints Phi (3 x 5), then dPhi/dfactor (3 x 5)
  */
 #include <stdio.h>
 #include <stdlib.h>
@@ -67,8 +69,43 @@ int main(int argc, char **argv) {
         refused += fes_ivp_host_f64(&d, NULL, NULL) < 0;
         refused += fes_ivp_host_f64(NULL, &b, NULL) < 0;
         refused += fes_num_dirs(FES_DING2003, 0, FES_DIR_U) < 0;
-        printf("refused %d of 10; e.g. \"%s\"\n", refused, fes_strerror(-1));
-        return refused == 10 ? 0 : 3;
+        /* the force factor rides with the X0 | U sets of the interval entry points only */
+        bad = d; bad.dirs = FES_DIR_X0 | FES_DIR_C; refused += fes_ivp_host_f64(&bad, &b, NULL) < 0;
+        /* per-scenario windows of 2^20 scenarios do not fit the static scratch: refused with its own code before any device work */
+        {
+            FesShootBuffers sb;
+            memset(&sb, 0, sizeof(sb));
+            bad = d; bad.flags = 0; bad.batch = 1 << 20; bad.dirs = FES_DIR_X0; bad.trace_every = 0; bad.trace_batch = 0;
+            refused += fes_shoot_static_f64(&bad, &sb, NULL) == -8 && strstr(fes_strerror(-8), "FES_STATIC_SCRATCH_BYTES") != NULL;
+        }
+        printf("refused %d of 12; e.g. \"%s\"\n", refused, fes_strerror(-1));
+        return refused == 12 ? 0 : 3;
+    }
+    if (argc > 1 && strcmp(argv[1], "--factor") == 0) {
+        /* node states: the rest state at every node; ctrl = one row per node, the factor fl*fv + fp of the interval */
+        double X[4][5], factor[3] = {1.0, 0.8, 1.15}, Phi[3][5], J[3][5][6];
+        FesShootBuffers sb;
+        for (int k = 0; k < 4; ++k) memcpy(X[k], x0, sizeof(x0));
+        memset(&sb, 0, sizeof(sb));
+        sb.params = params;
+        sb.X = X;
+        sb.stim_win = &win[0][0];
+        sb.ctrl = factor;
+        sb.Phi = Phi;
+        sb.J = J;
+        sb.j_cols = 6;
+        d.dirs = FES_DIR_X0 | FES_DIR_C;
+        d.flags |= FES_CTRL_SHARED;
+        d.trace_every = 0;
+        d.trace_batch = 0;
+        int rcf = fes_shoot_host_f64(&d, &sb, NULL);
+        if (rcf != 0) {
+            fprintf(stderr, "fes_shoot_host_f64 -> %d (%s)\n", rcf, fes_strerror(rcf));
+            return 10;
+        }
+        for (int k = 0; k < 3; ++k) for (int j = 0; j < 5; ++j) printf("%.17g\n", Phi[k][j]);
+        for (int k = 0; k < 3; ++k) for (int j = 0; j < 5; ++j) printf("%.17g\n", J[k][j][5]);
+        return 0;
     }
     int rc = fes_ivp_host_f64(&d, &b, NULL);
     if (rc != 0) {

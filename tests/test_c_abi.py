@@ -30,7 +30,7 @@ def test_library_is_self_contained_and_refuses_bad_arguments(client):
     assert "torch" not in deps and "python" not in deps.lower()
     r = subprocess.run([client, "--errors"], capture_output=True, text=True)
     assert r.returncode == 0, r.stdout + r.stderr
-    assert "refused 10 of 10" in r.stdout
+    assert "refused 12 of 12" in r.stdout
 
 
 @pytest.mark.skipif(torch.cuda.is_available(), reason="checks the behaviour WITHOUT a device")
@@ -45,3 +45,23 @@ def test_plain_c_call_reproduces_the_reference_golden(client):
     assert r.returncode == 0, r.stderr
     force = np.array([float(x) for x in r.stdout.split()])
     np.testing.assert_almost_equal(force, np.array(GOLD["F"]["ding2003_with_fatigue"]), decimal=GOLD["decimal"])
+
+
+@pytest.mark.gpu
+def test_plain_c_call_with_force_factor_matches_the_python_surface(client):
+    """fes_shoot_host_f64 with FES_DIR_X0 | FES_DIR_C from C: end points and dPhi/dfactor are those of fes.shoot(force_factor=)."""
+    from cocofest_b200 import fes
+
+    r = subprocess.run([client, "--factor"], capture_output=True, text=True)
+    assert r.returncode == 0, r.stderr
+    vals = np.array([float(x) for x in r.stdout.split()]).reshape(2, 3, 5)
+    dev = torch.device("cuda", 0)
+    pad = float(fes.PAD_TIME)
+    win = torch.tensor([[pad, pad, 0.0], [pad, 0.0, 0.1], [0.0, 0.1, 0.2]], dtype=torch.float64, device=dev)
+    p = torch.tensor(fes.default_params(fes.FES_DING2003), device=dev)
+    x0 = torch.tensor([0, 0, 3009, 0.050957, 0.103], dtype=torch.float64, device=dev)
+    X = x0[None, :, None].repeat(4, 1, 1).contiguous()
+    res = fes.shoot(fes.FES_DING2003, True, p, X, win, 0.3 / 3, n_steps=10, endpoints=True,   # the client's dt = 0.3 / 3
+                    force_factor=torch.tensor([1.0, 0.8, 1.15], dtype=torch.float64, device=dev))
+    assert np.array_equal(vals[0], res.Phi[:, :, 0].cpu().numpy())
+    assert np.array_equal(vals[1], res.Jc[:, :, 0].cpu().numpy())
