@@ -474,7 +474,7 @@ def shoot(kind, fatigue, params, X, win, dt, n_steps=10, ctrl=None, scheme=4, wa
     want: subset of {"x", "u", "p", "pf", "w"} selecting the Jacobian blocks.
     force_factor None | [ns] | [ns,B]: ``force_length * force_velocity + passive_force`` of ``f_dot_fun``
     (ding2003.py:309-311), held constant over each interval -- the seam for a caller that integrates the joint dynamics
-    of an FES-MSK model itself.  Such a call returns Jx, Ju and Jc = dPhi_k / d factor_k (want is ignored).
+    of an FES-MSK model itself.  Such a call returns Jx, Ju and Jc = dPhi_k / d factor_k (want must stay within {"x", "u"}).
     """
     X = torch.as_tensor(X)
     factor = force_factor is not None
@@ -489,6 +489,8 @@ def shoot(kind, fatigue, params, X, win, dt, n_steps=10, ctrl=None, scheme=4, wa
         raise ValueError(f"X must be [ns+1, {nx}, B]")
     if win.shape[0] < ns or (ctrl is not None and ctrl.shape[0] < ns):
         raise ValueError("stim window / controls have fewer rows than n_shooting")
+    if factor and not set(want) <= {"x", "u"}:
+        raise ValueError("a force_factor call returns Jx, Ju and Jc: the parameter / pulse-time blocks are not available with it")
     want = {"x", "u"} if factor else _normalise_want(kind, fatigue, nu, want)
     cx, cu, cp, cw, np_cols, passes = _shoot_layout(kind, fatigue, nx, nu, N, want, factor)
     cols = cx + cu + cp + cw + int(factor)
@@ -591,6 +593,8 @@ class ShootPlan:
         if (self.nu or self.factor) and ctrl is None:
             raise ValueError("this model needs controls: pass a template `ctrl` of the shape later calls will use")
         self._params, self._win, self._ctrl = params, win, ctrl
+        if self.factor and not set(want) <= {"x", "u"}:
+            raise ValueError("a force_factor plan returns Jx, Ju and Jc: the parameter / pulse-time blocks are not available with it")
         want = {"x", "u"} if self.factor else _normalise_want(kind, fatigue, self.nu, want)
         cx, cu, cp, cw, self.p_columns, passes = _shoot_layout(kind, fatigue, self.nx, self.nu, N, want, self.factor)
         self._cols = (cx, cu, cp, cw)

@@ -139,6 +139,9 @@ def test_oracle_force_factor_column_against_differences_of_the_numpy_restatement
 
 def test_force_factor_argument_checks():
     pb = random_problem("ding2007", B=4, N=5, ns=4, seed=35)
+    with pytest.raises(ValueError, match="Jx, Ju and Jc"):
+        fes.shoot(pb["kind"], pb["fat"], torch.tensor(pb["params"].T.copy()), torch.zeros((5, 2, 4), dtype=torch.float64),
+                  torch.tensor(pb["win"]), pb["dt"], ctrl=torch.tensor(pb["u"][0]), want=("x", "p"), force_factor=torch.ones(4, dtype=torch.float64))
     from tests.conftest import _load_emul
     from cocofest_b200 import _lib
     import ctypes
