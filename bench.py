@@ -495,7 +495,7 @@ def main():
     if world == 1 and not args.no_configs:
         del params_d, x0_d
         torch.cuda.empty_cache()
-        wanted = ["0", "1", "3", "4", "4c", "5", "5c", "5pf"]   # 5pf: the parameter columns of a fatigue model (reduced form, 2 x 2 propagator)
+        wanted = ["0", "1", "3", "4", "4c", "5", "5c", "5h", "5pf"]   # 5pf: the parameter columns of a fatigue model (reduced form, 2 x 2 propagator)
         configs, configs_meta = bc.run_configs(wanted, dev, "f64", steps=3, warmup=3, flush=flush)
         other = "f32" if not f32 else "f64"   # the headline workload in the other arithmetic type
         r2, _ = bc.run_configs(["2x0"], dev, other, steps=2, warmup=2, flush=flush, t2=args.final_time)

@@ -67,6 +67,13 @@ class FesIdentBuffers(Structure):
     ]
 
 
+class FesHessBuffers(Structure):
+    _fields_ = [
+        ("params", c_void_p), ("X", c_void_p), ("stim_win", c_void_p), ("ctrl", c_void_p), ("multipliers", c_void_p),
+        ("D2", c_void_p), ("H", c_void_p),
+    ]
+
+
 class FesIdentOptions(Structure):
     _fields_ = [("max_iter", c_int32), ("p_mask", c_int32), ("lambda0", c_double), ("ftol", c_double), ("xtol", c_double)]
 
@@ -84,6 +91,9 @@ PROTOTYPES = {
     "fes_shoot_f64": (c_int, [POINTER(FesDesc), POINTER(FesShootBuffers), c_void_p]),
     "fes_shoot_f32": (c_int, [POINTER(FesDesc), POINTER(FesShootBuffers), c_void_p]),
     "fes_shoot_static_f64": (c_int, [POINTER(FesDesc), POINTER(FesShootBuffers), c_void_p]),
+    "fes_shoot_hess_num_dirs": (c_int, [c_int, c_int, c_int, c_int]),
+    "fes_shoot_hess_f64": (c_int, [POINTER(FesDesc), POINTER(FesHessBuffers), c_void_p]),
+    "fes_shoot_hess_host_f64": (c_int, [POINTER(FesDesc), POINTER(FesHessBuffers), c_void_p]),
     "fes_ivp_host_f64": (c_int, [POINTER(FesDesc), POINTER(FesIvpBuffers), c_void_p]),
     "fes_ivp_host_f32": (c_int, [POINTER(FesDesc), POINTER(FesIvpBuffers), c_void_p]),
     "fes_shoot_host_f64": (c_int, [POINTER(FesDesc), POINTER(FesShootBuffers), c_void_p]),

@@ -9,6 +9,7 @@
 #include "fes_b200.h"
 #include "fes_kernels.cuh"
 #include "fes_ident.cuh"
+#include "fes_hess.cuh"
 
 namespace fes {
 namespace abi {
@@ -203,6 +204,58 @@ void fill_ident_args(const FesDesc *d, const FesIdentBuffers *b, const FesIdentO
     a.lambda0 = (T)o->lambda0;
     a.ftol = (T)o->ftol;
     a.xtol = (T)o->xtol;
+}
+
+// ---- second-order tangents (fes_shoot_hess_f64) ------------------------------------------------------------------------
+// directions z = (x, the model's controls [, force factor]); desc->dirs must be X0 | U or X0 | U | C (U is ignored for ding2003)
+inline int hess_num_dirs(const FesDesc *d) {
+    return (d->fatigue ? 5 : 2) + num_controls(d->model_kind, d->n_trunc) + ((d->dirs & FES_DIR_C) ? 1 : 0);
+}
+inline int check_hess(const FesDesc *d, const FesHessBuffers *b) {
+    if (d == nullptr || d->abi_version != FES_ABI_VERSION) return E_DESC;
+    if (d->model_kind < 0 || d->model_kind > 2 || (d->fatigue != 0 && d->fatigue != 1)) return E_MODEL;
+    if (d->scheme != 1 && d->scheme != 2 && d->scheme != 4) return E_MODEL;
+    if (d->n_trunc < 1 || d->n_trunc > (d->model_kind == FES_HMED2018 ? 64 : 1024) || d->n_shooting < 1 || d->n_steps < 1 ||
+        d->n_steps > 256)
+        return E_SIZE;
+    if (d->batch < 1 || !(d->dt > 0.0) || !(d->tauc > 0.0)) return E_SIZE;
+    if ((d->dirs & ~(FES_DIR_C | FES_DIR_U)) != FES_DIR_X0) return E_DIRS;
+    if (d->model_kind != FES_DING2003 && !(d->dirs & FES_DIR_U)) return E_DIRS;  // all of z or nothing
+    if (b == nullptr || b->params == nullptr || b->X == nullptr || b->stim_win == nullptr) return E_BUF;
+    if (num_controls(d->model_kind, d->n_trunc) + ((d->dirs & FES_DIR_C) ? 1 : 0) > 0 && b->ctrl == nullptr) return E_BUF;
+    if (b->D2 == nullptr && b->H == nullptr) return E_BUF;
+    if (b->H != nullptr && b->multipliers == nullptr) return E_BUF;
+    return E_OK;
+}
+inline void fill_hess_args(const FesDesc *d, const FesHessBuffers *b, HessArgs &a) {
+    std::memset(&a, 0, sizeof(a));
+    a.params = (const double *)b->params;
+    a.pB = (d->flags & FES_PARAMS_SHARED) ? 1 : d->batch;
+    a.pS = (d->flags & FES_PARAMS_SHARED) ? 0 : 1;
+    a.X = (const double *)b->X;
+    a.win = b->stim_win;
+    a.wB = (d->flags & FES_WIN_SHARED) ? 1 : d->batch;
+    a.wS = (d->flags & FES_WIN_SHARED) ? 0 : 1;
+    a.ctrl = (const double *)b->ctrl;
+    a.cB = (d->flags & FES_CTRL_SHARED) ? 1 : d->batch;
+    a.cS = (d->flags & FES_CTRL_SHARED) ? 0 : 1;
+    a.factor = (d->dirs & FES_DIR_C) ? 1 : 0;
+    a.nur = num_controls(d->model_kind, d->n_trunc) + a.factor;
+    a.lam = (const double *)b->multipliers;
+    a.D2 = (double *)b->D2;
+    a.H = (double *)b->H;
+    a.B = d->batch;
+    a.N = d->n_trunc;
+    a.ns = d->n_shooting;
+    a.S = d->n_steps;
+    a.scheme = d->scheme;
+    a.nz = hess_num_dirs(d);
+    a.npairs = a.nz * (a.nz + 1) / 2;
+    a.h = d->dt / d->n_steps;
+    a.dt = d->dt;
+    a.t_start = d->t_start;
+    a.tauc = d->tauc;
+    a.r0_km = d->r0_km;
 }
 
 inline const char *strerror_abi(int code) {

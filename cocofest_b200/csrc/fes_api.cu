@@ -131,6 +131,17 @@ int ident_impl(const FesDesc *d, const FesIdentBuffers *b, const FesIdentOptions
     return rc;
 }
 
+// ---- fes_shoot_hess_f64: second-order tangents of the interval map (fes_hess.cuh) ---------------------------------------
+int hess_impl(const FesDesc *d, const FesHessBuffers *b, void *stream) {
+    int rc = check_hess(d, b);
+    if (rc) return rc;
+    HessArgs a;
+    fill_hess_args(d, b, a);
+    rc = launch_hess(d->model_kind, d->fatigue, a, (cudaStream_t)stream);
+    if (rc == 0) ++g_launches;
+    return rc;
+}
+
 // ---- fes_shoot_static_f64: the interval kernel with its tables in library-owned static device memory ----------------------
 // For callers that cannot allocate (stream capture, serving loops).  The scratch is a file-scope device array: every GPU that
 // loads the library holds FES_STATIC_SCRATCH_BYTES of it until the process exits.  In host code the name `g_static_scratch` is
@@ -383,6 +394,47 @@ int shoot_host_impl(const FesDesc *d, const FesShootBuffers *h, void *stream) {
     return pool.finish();
 }
 
+int hess_host_impl(const FesDesc *d, const FesHessBuffers *h, void *stream) {
+    int rc = check_hess(d, h);
+    if (rc) return rc;
+    cudaStream_t s = (cudaStream_t)stream;
+    const size_t nx = d->fatigue ? 5 : 2, nur = num_controls(d->model_kind, d->n_trunc) + ((d->dirs & FES_DIR_C) ? 1 : 0);
+    const size_t B = (size_t)d->batch, ns = (size_t)d->n_shooting, N = (size_t)d->n_trunc;
+    const size_t nz = (size_t)hess_num_dirs(d), npairs = nz * (nz + 1) / 2;
+    DevPool pool(s);
+    Staged in[5] = {
+        {nullptr, h->params, sizeof(double) * FES_NP * ((d->flags & FES_PARAMS_SHARED) ? 1 : B)},
+        {nullptr, h->X, sizeof(double) * (ns + 1) * nx * B},
+        {nullptr, h->stim_win, sizeof(double) * ns * N * ((d->flags & FES_WIN_SHARED) ? 1 : B)},
+        {nullptr, h->ctrl, nur ? sizeof(double) * ns * nur * ((d->flags & FES_CTRL_SHARED) ? 1 : B) : 0},
+        {nullptr, h->multipliers, (h->H && h->multipliers) ? sizeof(double) * ns * nx * B : 0},
+    };
+    for (Staged &st : in) st.dev = pool.alloc(st.bytes);
+    const size_t b_d2 = h->D2 ? sizeof(double) * ns * nx * npairs * B : 0, b_h = h->H ? sizeof(double) * ns * npairs * B : 0;
+    FesHessBuffers g;
+    std::memset(&g, 0, sizeof(g));
+    g.D2 = pool.alloc(b_d2);
+    g.H = pool.alloc(b_h);
+    t_last = HostTiming();
+    t_last.alloc = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - pool.t0).count();
+    pool.mark(0);
+    for (Staged &st : in) pool.upload_to(st.dev, st.host, st.bytes);
+    pool.mark(1);
+    if (pool.err) return pool.err;
+    g.params = in[0].dev;
+    g.X = in[1].dev;
+    g.stim_win = (const double *)in[2].dev;
+    g.ctrl = in[3].dev;
+    g.multipliers = in[4].dev;
+    rc = hess_impl(d, &g, stream);
+    if (rc) return rc;
+    pool.mark(2);
+    pool.download(h->D2, g.D2, b_d2);
+    pool.download(h->H, g.H, b_h);
+    pool.mark(3);
+    return pool.finish();
+}
+
 template <typename T>
 int ident_host_impl(const FesDesc *d, const FesIdentBuffers *h, const FesIdentOptions *o, void *stream) {
     int rc = check_ident(d, h, o);
@@ -538,6 +590,12 @@ int fes_ivp_f32(const FesDesc *d, const FesIvpBuffers *b, void *s) { return ivp_
 int fes_shoot_f64(const FesDesc *d, const FesShootBuffers *b, void *s) { return shoot_impl<double>(d, b, s); }
 int fes_shoot_f32(const FesDesc *d, const FesShootBuffers *b, void *s) { return shoot_impl<float>(d, b, s); }
 int fes_shoot_static_f64(const FesDesc *d, const FesShootBuffers *b, void *s) { return shoot_static_impl(d, b, s); }
+int fes_shoot_hess_num_dirs(int model_kind, int fatigue, int n_trunc, int dirs) {
+    if (model_kind < 0 || model_kind > 2 || n_trunc < 1) return -1;
+    return (fatigue ? 5 : 2) + num_controls(model_kind, n_trunc) + ((dirs & FES_DIR_C) ? 1 : 0);
+}
+int fes_shoot_hess_f64(const FesDesc *d, const FesHessBuffers *b, void *s) { return hess_impl(d, b, s); }
+int fes_shoot_hess_host_f64(const FesDesc *d, const FesHessBuffers *b, void *s) { return hess_host_impl(d, b, s); }
 int fes_ivp_host_f64(const FesDesc *d, const FesIvpBuffers *b, void *s) { return ivp_host_impl<double>(d, b, s); }
 int fes_ivp_host_f32(const FesDesc *d, const FesIvpBuffers *b, void *s) { return ivp_host_impl<float>(d, b, s); }
 int fes_shoot_host_f64(const FesDesc *d, const FesShootBuffers *b, void *s) { return shoot_host_impl<double>(d, b, s); }

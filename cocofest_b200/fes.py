@@ -560,6 +560,74 @@ def shoot(kind, fatigue, params, X, win, dt, n_steps=10, ctrl=None, scheme=4, wa
     return ShootResult(G, Phi, Jx, Ju, Jp, Jw, tuple(np_cols), Jc)
 
 
+@dataclass
+class HessResult:
+    D2: torch.Tensor | None     # [ns, nx, npairs, B]   d2 Phi_k[r] / dz_i dz_j, pairs i <= j along the upper triangle
+    H: torch.Tensor | None      # [ns, npairs, B]       sum_r multipliers[k, r] D2[k, r]
+    nz: int                     # z = (x, the model's controls [, force factor])
+
+    def pair_index(self) -> torch.Tensor:
+        """[nz, nz] long tensor: the packed position of entry (i, j) (symmetric)."""
+        nz = self.nz
+        iu = torch.triu_indices(nz, nz)
+        idx = torch.zeros((nz, nz), dtype=torch.long)
+        idx[iu[0], iu[1]] = torch.arange(iu.shape[1])
+        idx[iu[1], iu[0]] = torch.arange(iu.shape[1])
+        return idx
+
+    def full(self, packed=None) -> torch.Tensor:
+        """Packed pairs -> full symmetric blocks: D2 [ns, nx, nz, nz, B] (default) or H [ns, nz, nz, B]."""
+        t = self.D2 if packed is None else packed
+        idx = self.pair_index().to(t.device)
+        return t.index_select(-2, idx.reshape(-1)).reshape(*t.shape[:-2], self.nz, self.nz, t.shape[-1])
+
+
+def shoot_hessian(kind, fatigue, params, X, win, dt, n_steps=10, ctrl=None, scheme=4, multipliers=None, second=True,
+                  t_start=0.0, tauc=None, r0_km=R0_KM_RELATIONSHIP, force_factor=None) -> HessResult:
+    """Exact second derivatives of every interval map with respect to z_k = (x_k, u_k [, factor_k]): what casadi's exact
+    Hessian of the continuity rows consists of (bioptim interfaces/ipopt_options.py:88, penalty.py:1056-1105).
+
+    Arguments as ``shoot`` (fp64).  multipliers [ns, nx, B]: also returns H = sum_r multipliers[k, r] d2 Phi_k[r]; the
+    continuity rows are g_k = x_{k+1} - Phi_k, so their part of the Hessian of the Lagrangian is -H.  second=False skips
+    the full tensor D2 (a solver iteration needs H only).  One kernel launch, no workspace."""
+    X = torch.as_tensor(X)
+    factor = force_factor is not None
+    if factor:
+        Xt = _prep(X, torch.float64, X.device)
+        ctrl = _with_factor(ctrl, force_factor, _nu(kind, torch.as_tensor(win).shape[1]), Xt.shape[0] - 1, Xt.shape[-1], torch.float64, Xt.device)
+    device, dtype, B, N, flags, params, win, ctrl = _common(kind, fatigue, params, win, ctrl, X, torch.float64, extra_ctrl_rows=int(factor))
+    nx, nu = _nx(fatigue), _nu(kind, N)
+    X = _prep(X, dtype, device)
+    ns = X.shape[0] - 1
+    if X.dim() != 3 or X.shape[1] != nx or ns < 1:
+        raise ValueError(f"X must be [ns+1, {nx}, B]")
+    if win.shape[0] < ns or (ctrl is not None and ctrl.shape[0] < ns):
+        raise ValueError("stim window / controls have fewer rows than n_shooting")
+    if ctrl is not None and ctrl.shape[0] != ns:
+        ctrl = ctrl[:ns].contiguous()
+    if multipliers is None and not second:
+        raise ValueError("nothing to compute: pass multipliers or keep second=True")
+    lam = None
+    if multipliers is not None:
+        lam = _prep(multipliers, dtype, device)
+        if tuple(lam.shape) != (ns, nx, B):
+            raise ValueError(f"multipliers must be [{ns}, {nx}, {B}]")
+    nz = nx + nu + int(factor)
+    npairs = nz * (nz + 1) // 2
+    D2 = _empty((ns, nx, npairs, B), dtype, device) if second else None
+    H = _empty((ns, npairs, B), dtype, device) if lam is not None else None
+    dirs = FES_DIR_X0 | FES_DIR_U | (FES_DIR_C if factor else 0)
+    desc = _desc(kind, fatigue, scheme, N, ns, n_steps, dirs, flags, B, dt, t_start, tauc, r0_km)
+    buf = _lib.FesHessBuffers(_ptr(params), _ptr(X), _ptr(win), _ptr(ctrl), _ptr(lam), _ptr(D2), _ptr(H))
+    L = _lib.lib()
+    if device.type == "cuda":
+        with torch.cuda.device(device):
+            _lib.check(L.fes_shoot_hess_f64(ctypes.byref(desc), ctypes.byref(buf), ctypes.c_void_p(_stream_ptr(device))), "fes_shoot_hess")
+    else:
+        _lib.check(L.fes_shoot_hess_host_f64(ctypes.byref(desc), ctypes.byref(buf), None), "fes_shoot_hess_host")
+    return HessResult(D2, H, nz)
+
+
 class ShootPlan:
     """One multiple-shooting evaluation (defects + the requested Jacobian blocks of B scenarios x ns intervals) set up
     ONCE and called once per solver iteration -- what a built OCP is to the reference (``prepare_ocp`` builds the casadi

@@ -84,8 +84,11 @@ class FesShooting:
     # typical magnitudes of (Cn, F, A, Tau1, Km) and of the controls: floors of the finite-difference steps
     _STATE_SCALE = (0.1, 10.0, 1000.0, 0.05, 0.1)
 
-    def second_derivatives(self, X, U=None, params=None, rel_step=1e-5):
-        """d2 Phi_k / d z_k d z_k for z_k = (x_k, u_k): tensor [ns, nx, nz, nz, B], nz = nx + nu.
+    def second_derivatives(self, X, U=None, params=None, rel_step=1e-5, method="exact", force_factor=None):
+        """d2 Phi_k / d z_k d z_k for z_k = (x_k, u_k): tensor [ns, nx, nz, nz, B], nz = nx + nu (+ 1 with force_factor).
+
+        method="exact" (default): the second-order tangent kernel (``fes.shoot_hessian`` -> fes_shoot_hess_f64), one launch,
+        exact to rounding.  method="fd": the route below, kept as an independent check and for float32 plans.
 
         The reference's Ipopt runs on casadi's exact Hessian by default (bioptim interfaces/ipopt_options.py:88).  The
         kernels propagate first-order tangents only; this evaluates the second derivatives as CENTRAL DIFFERENCES OF THE
@@ -94,6 +97,12 @@ class FesShooting:
         is O(rel_step^2) truncation + O(1e-16 / rel_step) rounding: ~1e-10 relative at the default step (measured against
         complex-step differentiation of the oracle, tests/test_second_derivatives.py).  Not a second-order tangent
         propagation; DESIGN.md section 8 lists that as open."""
+        if method not in ("exact", "fd"):
+            raise ValueError("method must be 'exact' or 'fd'")
+        if method == "exact":
+            return self.hessian(X, U, params, force_factor=force_factor).full()
+        if force_factor is not None:
+            raise ValueError("the finite-difference route does not carry the force factor: use method='exact'")
         X = torch.as_tensor(X).to(self.device).contiguous()
         ns, nx, nu = self.n_shooting, self.nx, self.nu
         B = X.shape[-1]
@@ -128,6 +137,16 @@ class FesShooting:
                 h = (Up[:, j] - Um[:, j]) * 0.5
                 out[:, :, :, d] = (jac(X, Up) - jac(X, Um)) / (2.0 * h[:, None, None, :])
         return 0.5 * (out + out.transpose(2, 3))
+
+    def hessian(self, X, U=None, params=None, multipliers=None, second=True, force_factor=None) -> _fes.HessResult:
+        """Exact second derivatives in packed form (``fes.HessResult``): D2 [ns, nx, npairs, B] and, with ``multipliers``
+        [ns, nx, B], H [ns, npairs, B] = sum_r lambda[k, r] d2 Phi_k[r] -- one launch per solver iteration
+        (``second=False`` skips D2).  ``.full()`` / ``.full(res.H)`` give the symmetric blocks."""
+        X = torch.as_tensor(X).to(self.device)
+        return _fes.shoot_hessian(self.model.kind, self.model.with_fatigue, self._params(params), X, self.window[:self.n_shooting],
+                                  self.dt, n_steps=self.n_steps, ctrl=U, scheme=self.scheme, multipliers=multipliers,
+                                  second=second, t_start=self.t_start, tauc=self.model.tauc,
+                                  r0_km=self.model.r0_km_relationship, force_factor=force_factor)
 
     @staticmethod
     def lagrangian_hessian(multipliers, second):

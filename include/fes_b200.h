@@ -164,6 +164,20 @@ typedef struct FesIdentBuffers {
     int64_t workspace_bytes;
 } FesIdentBuffers;
 
+/* Buffers of one second-order call (fes_shoot_hess_f64).  Directions z = (x_k, u_k [, c_k]): the nx states of node k, the
+ * model's controls of interval k (none | pulse width | the N pulse intensities of the window) and, with FES_DIR_C, the force
+ * factor; nz = nx + nu (+ 1).  Pairs (i <= j) are numbered along the upper triangle, row-major: p = 0 is (0,0), p = 1 is
+ * (0,1), ..., p = nz is (1,1), ...; npairs = nz (nz + 1) / 2. */
+typedef struct FesHessBuffers {
+    const void *params;      /* [FES_NP][B] | [FES_NP]                                              */
+    const void *X;           /* [ns+1][nx][B]  decision states at nodes                             */
+    const double *stim_win;  /* [>=ns][N][B] | [>=ns][N]                                            */
+    const void *ctrl;        /* [ns][nu][B] | [ns][nu] | NULL; nu + 1 rows with FES_DIR_C           */
+    const void *multipliers; /* [ns][nx][B]  lambda of the continuity rows | NULL when H is NULL    */
+    void *D2;                /* [ns][nx][npairs][B]  d2 Phi_k[r] / dz_i dz_j | NULL                  */
+    void *H;                 /* [ns][npairs][B]  sum_r lambda[k][r] d2 Phi_k[r] / dz_i dz_j | NULL   */
+} FesHessBuffers;
+
 typedef struct FesIdentOptions {
     int32_t max_iter; /* Levenberg-Marquardt iterations; 0 = evaluate cost / gradient / Gauss-Newton matrix only */
     int32_t p_mask;   /* bit d set = P-column d is identified (key_parameter_to_identify)                      */
@@ -209,6 +223,16 @@ int fes_shoot_f32(const FesDesc *desc, const FesShootBuffers *buf, void *stream)
 #define FES_STATIC_SCRATCH_BYTES (4 * 1024 * 1024)
 int fes_shoot_static_f64(const FesDesc *desc, const FesShootBuffers *buf, void *stream);
 
+/* Second derivatives of the interval map, d2 Phi_k / dz_k dz_k, for an exact-Hessian solver: the reference's Ipopt default
+ * is casadi's exact Hessian of the Lagrangian (external/bioptim/bioptim/interfaces/ipopt_options.py:88), i.e. casadi's second
+ * derivative of the unrolled integrator inside every continuity row (external/bioptim/bioptim/limits/penalty.py:1056-1105).
+ * One thread per (scenario, interval, pair of directions), hyper-dual arithmetic through the same RK stages: the exact
+ * second-order tangent of the discrete map.  desc->dirs = FES_DIR_X0 | FES_DIR_U [| FES_DIR_C]; fp64 only; needs no workspace
+ * (desc->tile_offset, trace fields and FES_TABLES_READY are ignored) and allocates nothing.  The contribution of the
+ * continuity rows g_k = x_{k+1} - Phi_k to the Hessian of the Lagrangian is MINUS buf->H. */
+int fes_shoot_hess_num_dirs(int model_kind, int fatigue, int n_trunc, int dirs);
+int fes_shoot_hess_f64(const FesDesc *desc, const FesHessBuffers *buf, void *stream);
+
 /* Force-tracking cost (fes_identification_ocp.py:248-266) with its gradient and Gauss-Newton matrix, and the
  * bounded Levenberg-Marquardt identification of the P-group parameters (fes_identification_ocp.py:269-299), one
  * thread per candidate, whole loop on device.  desc->dirs must be FES_DIR_P, desc->fatigue 0. */
@@ -222,6 +246,7 @@ int fes_shoot_host_f64(const FesDesc *desc, const FesShootBuffers *host_buf, voi
 int fes_shoot_host_f32(const FesDesc *desc, const FesShootBuffers *host_buf, void *stream);
 int fes_identify_host_f64(const FesDesc *desc, const FesIdentBuffers *host_buf, const FesIdentOptions *opt, void *stream);
 int fes_identify_host_f32(const FesDesc *desc, const FesIdentBuffers *host_buf, const FesIdentOptions *opt, void *stream);
+int fes_shoot_hess_host_f64(const FesDesc *desc, const FesHessBuffers *host_buf, void *stream);
 
 /* Roofline denominators measured on the device the caller made current: runs `launches` launches of a
  * register-only FMA kernel on `stream` and returns the best FMA-flop rate (2 flop per FMA) in TFLOP/s. */

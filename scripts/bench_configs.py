@@ -257,7 +257,7 @@ def run_configs(wanted, dev, dtype="f64", steps=3, warmup=3, scale=1.0, flush=No
                  "best_cost": float(out.cost[out.best()].item())})
         del p, x0
 
-    if {"5", "5pf", "5c"} & set(wanted):
+    if {"5", "5pf", "5c", "5h"} & set(wanted):
         B = max(1024, int((1 << 16) * scale))
         proto, p, X, U = protocols.nmpc_scenarios(B, device=dev)
         p, X, U = p.to(dt_t), X.to(dt_t), U.to(dt_t)
@@ -288,6 +288,27 @@ def run_configs(wanted, dev, dtype="f64", steps=3, warmup=3, scale=1.0, flush=No
             add("5c: the same horizon with the force factor fl*fv + fp per interval as an input, + dPhi/dfactor (ShootPlan call)",
                 kernel_name("shoot", dtype, fes.FES_DING2007, True, fes.FES_DIR_X0 | fes.FES_DIR_U | fes.FES_DIR_C), B * ns * S, ms, ob,
                 (X.numel() + ext.numel()) * esz, dtype, {"scenarios": B, "n_shooting": ns})
+        if "5h" in wanted and dtype == "f64":
+            # one exact-Hessian solver iteration's worth of second derivatives: H_k = sum_r lambda_kr d2 Phi_kr / dz dz for every
+            # interval (21 pairs of (x, pw) each), one launch of the second-order tangent kernel (fes_hess.cuh); beside it the
+            # route it replaces, central differences of the exact Jacobian (2 nz = 12 ShootPlan calls)
+            g = torch.Generator(device="cpu").manual_seed(7)
+            lam = torch.empty((ns, 5, B), dtype=torch.float64).normal_(generator=g).to(dev)
+            fn = lambda: fes.shoot_hessian(fes.FES_DING2007, True, p, X, win, proto["dt"], n_steps=S, ctrl=U, multipliers=lam, second=False)
+            out, ms = timed(fn, steps, warmup, flush)
+            plan_fd = fes.ShootPlan(fes.FES_DING2007, True, p, win, proto["dt"], ns, B, n_steps=S, ctrl=U, want=("x", "u"), defects=False, dtype=dt_t)
+
+            def fd_route():
+                for _ in range(12):
+                    r = plan_fd(X, U)
+                return r
+            _, ms_fd = timed(fd_route, steps, warmup, flush)
+            add("5h: the same horizon, exact Hessian blocks sum_r lambda_r d2Phi_r/dz dz (21 pairs per interval) in one launch: second-order tangents, one thread per (scenario, interval, pair)",
+                "fes_hess_kernel<DING2007, fatigue, X0|U> (no static count: the step is not one basic block)", B * ns * S, ms,
+                out.H.numel() * 8, (X.numel() + U.numel() + lam.numel()) * 8, dtype,
+                {"scenarios": B, "n_shooting": ns, "pairs": out.H.shape[1], "pair_steps_per_s": B * ns * S * out.H.shape[1] / (statistics.mean(ms) * 1e-3),
+                 "finite_difference_route_ms": statistics.mean(ms_fd),
+                 "finite_difference_route": "12 ShootPlan calls (central differences of the exact Jacobian, ~1e-10), arithmetic of the differences not included"})
         if "5pf" in wanted:
             # the dense parameter columns of a fatigue model (what a fatigue-parameter identification would differentiate)
             fn = lambda: fes.shoot(fes.FES_DING2007, True, p, X, win, proto["dt"], n_steps=S, ctrl=U, want=("p", "pf"),

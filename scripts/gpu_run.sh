@@ -15,6 +15,7 @@
 #                    scripts/bench_configs.py --configs $VCFG --dtype $VDT (defaults 2x0, f32), 60 s protocol
 #   scale<N>         torchrun bench.py --gpus N (needs gpurun --gpus N)
 #   ncu_list         launch list of the default bench command (after a plain run of it)
+#   hess             tests/test_second_order_kernel.py on the GPU + config 5h (exact Hessian blocks)
 #   ncu_full:<cfg>   ncu --set full of the top kernel of scripts/bench_configs.py --configs <cfg>  (2x0 = headline kernel)
 #   san_memcheck | san_racecheck | san_synccheck   compute-sanitizer on the small parity problems (scripts/sanitize_cases.py)
 set -u
@@ -41,9 +42,14 @@ for stage in "$@"; do
           python -c "import sys, json; d = json.loads(sys.stdin.read()); print(json.dumps({'batch': d['config']['batch_per_gpu'], 'value': d['value'], 'ms': d['ms_per_step'], 'pipe': d['roofline']['pipe']['frac_of_nominal'] if d['roofline']['pipe'] else None}))" | tee -a gpurun_out/strong1_$tag.jsonl
       done ;;
     configs)
-      timeout 900 python scripts/bench_configs.py --configs 1,2fwd,3,4,4b,4c,5,5c,5pf > gpurun_out/configs_f64_$tag.jsonl 2> gpurun_out/configs_f64_$tag.err; echo "rc=$?"
+      timeout 900 python scripts/bench_configs.py --configs 1,2fwd,3,4,4b,4c,5,5c,5h,5pf > gpurun_out/configs_f64_$tag.jsonl 2> gpurun_out/configs_f64_$tag.err; echo "rc=$?"
       timeout 900 python scripts/bench_configs.py --configs 1,2fwd,2x0,3,4,4b,4c,5,5c,5pf --dtype f32 > gpurun_out/configs_f32_$tag.jsonl 2> gpurun_out/configs_f32_$tag.err; echo "rc=$?"
       cut -c1-260 gpurun_out/configs_f64_$tag.jsonl gpurun_out/configs_f32_$tag.jsonl ;;
+    hess)
+      timeout 600 python -m pytest tests/test_second_order_kernel.py tests/test_second_derivatives.py tests/test_api_surface.py -m gpu -q > gpurun_out/pytest_hess_$tag.log 2>&1; echo "pytest rc=$?" >> gpurun_out/pytest_hess_$tag.log
+      tail -4 gpurun_out/pytest_hess_$tag.log
+      timeout 600 python scripts/bench_configs.py --configs 5,5h > gpurun_out/configs_hess_$tag.jsonl 2> gpurun_out/configs_hess_$tag.err; echo "rc=$?"
+      cut -c1-900 gpurun_out/configs_hess_$tag.jsonl ;;
     margin)
       timeout 900 python scripts/parity_margin.py > gpurun_out/parity_margin_$tag.txt 2>&1; echo "margin rc=$?"; cat gpurun_out/parity_margin_$tag.txt ;;
     sweep)
@@ -72,7 +78,7 @@ for l in sys.stdin:
       echo "ncu_list rc=$?"; tail -3 gpurun_out/launches_bench_$tag.csv ;;
     ncu_full:*)
       cfg=${stage#ncu_full:}; dt=f64; case $cfg in *@f32) dt=f32; cfg=${cfg%@f32};; esac
-      pat=fes_ivp_kernel; case $cfg in 4b|4c) pat=fes_ident_kernel;; 5|5c|5pf) pat=fes_shoot_kernel;; esac
+      pat=fes_ivp_kernel; case $cfg in 4b|4c) pat=fes_ident_kernel;; 5|5c|5pf) pat=fes_shoot_kernel;; 5h) pat=fes_hess_kernel;; esac
       cmd="python scripts/bench_configs.py --configs $cfg --dtype $dt --steps 1 --warmup 1 --t2 ${T2:-300}"
       timeout 600 $cmd > gpurun_out/ncu_full_plain_${cfg}_${dt}_$tag.log 2>&1 &&
       timeout 1500 ncu --set full --clock-control none --import-source on -k regex:$pat -s 1 -c 1 -f -o gpurun_out/prof_${cfg}_${dt}_$tag $cmd > gpurun_out/ncu_full_${cfg}_${dt}_$tag.log 2>&1

@@ -28,6 +28,9 @@ GROUP_BITS = ((1, "X0"), (2, "U"), (32, "C"), (4, "P"), (16, "PF"), (8, "W"))
 
 def pretty(sym):
     """_ZN3fes14fes_ivp_kernelIdLi0ELb1ELi1EEEvNS_7IvpArgsIT_EE -> fes_ivp_kernel<double, DING2003, fatigue, X0>"""
+    h = re.match(r"_ZN3fes\d+fes_hess_kernelILi(\d)ELb([01])ELb([01])EEE", sym)
+    if h:   # fes_hess_kernel<KIND, FAT, FC>: the second-order tangent kernel (fp64 only)
+        return f"fes_hess_kernel<{KIND.get(h.group(1), h.group(1))}, {'fatigue' if h.group(2) == '1' else 'no_fatigue'}, {'X0|U|C' if h.group(3) == '1' else 'X0|U'}>"
     m = re.match(r"_ZN3fes\d+(fes_\w+_kernel)I([df])(?:Li(\d)E)?(?:Lb([01])E)?(?:Li(\d+)E)?", sym)
     if not m:
         return sym

@@ -273,6 +273,17 @@ int ident_host(const FesDesc *d, const FesIdentBuffers *b, const FesIdentOptions
 }
 }  // namespace
 
+// second-order tangents: the same hess_unit template, plain loops over (interval, pair, scenario)
+template <int KIND, bool FAT>
+static void hess_cpu_kf(const HessArgs &a) {
+    for (int k = 0; k < a.ns; ++k)
+        for (int p = 0; p < a.npairs; ++p)
+            for (int64_t b = 0; b < a.B; ++b) {
+                if (a.factor) hess_store<KIND, FAT, true>(a, k, p, b);
+                else hess_store<KIND, FAT, false>(a, k, p, b);
+            }
+}
+
 extern "C" {
 int fes_version(void) { return FES_ABI_VERSION; }
 const char *fes_strerror(int code) { const char *m = strerror_abi(code); return m ? m : "unknown error"; }
@@ -305,6 +316,27 @@ int fes_shoot_static_f64(const FesDesc *d, const FesShootBuffers *b, void *) {
     bb.workspace_bytes = FES_STATIC_SCRATCH_BYTES;
     return shoot_impl<double>(d, &bb);
 }
+
+int fes_shoot_hess_num_dirs(int k, int f, int n, int dirs) {
+    if (k < 0 || k > 2 || n < 1) return -1;
+    return (f ? 5 : 2) + num_controls(k, n) + ((dirs & FES_DIR_C) ? 1 : 0);
+}
+int fes_shoot_hess_f64(const FesDesc *d, const FesHessBuffers *b, void *) {
+    const int rc = check_hess(d, b);
+    if (rc) return rc;
+    HessArgs a;
+    fill_hess_args(d, b, a);
+    switch (d->model_kind * 2 + d->fatigue) {
+        case 0: hess_cpu_kf<DING2003, false>(a); break;
+        case 1: hess_cpu_kf<DING2003, true>(a); break;
+        case 2: hess_cpu_kf<DING2007, false>(a); break;
+        case 3: hess_cpu_kf<DING2007, true>(a); break;
+        case 4: hess_cpu_kf<HMED2018, false>(a); break;
+        default: hess_cpu_kf<HMED2018, true>(a); break;
+    }
+    return 0;
+}
+int fes_shoot_hess_host_f64(const FesDesc *d, const FesHessBuffers *b, void *s) { return fes_shoot_hess_f64(d, b, s); }
 
 // host-buffer entry points: same loops, workspace allocated here
 #define HOST_VARIANT(name, impl, T, Buf)                                                      \
