@@ -6,6 +6,7 @@
  *
  *   abi_client            run the case; exit code 0, or 10 + (library return code != 0)
  *   abi_client --errors   exercise the argument checks only (no device work): exit 0 when every bad call is refused
+ *   abi_client --hess     the three intervals through fes_shoot_hess_host_f64 (second derivatives contracted with multipliers of one)
  *   abi_client --factor   the three intervals of the same case through fes_shoot_host_f64 with the force factor of every
  *                         interval as an input (FES_DIR_X0 | FES_DIR_C): prints Phi (3 x 5), then dPhi/dfactor (3 x 5)
  */
@@ -78,8 +79,17 @@ int main(int argc, char **argv) {
             bad = d; bad.flags = 0; bad.batch = 1 << 20; bad.dirs = FES_DIR_X0; bad.trace_every = 0; bad.trace_batch = 0;
             refused += fes_shoot_static_f64(&bad, &sb, NULL) == -8 && strstr(fes_strerror(-8), "FES_STATIC_SCRATCH_BYTES") != NULL;
         }
-        printf("refused %d of 12; e.g. \"%s\"\n", refused, fes_strerror(-1));
-        return refused == 12 ? 0 : 3;
+        /* the second-order entry point wants all of z = (x, u): a parameter direction set is refused before any device work */
+        {
+            FesHessBuffers hb;
+            double dummy[1];
+            memset(&hb, 0, sizeof(hb));
+            hb.params = params; hb.X = dummy; hb.stim_win = &win[0][0]; hb.D2 = dummy;
+            bad = d; bad.dirs = FES_DIR_P; bad.trace_every = 0; bad.trace_batch = 0;
+            refused += fes_shoot_hess_host_f64(&bad, &hb, NULL) == -4;
+        }
+        printf("refused %d of 13; e.g. \"%s\"\n", refused, fes_strerror(-1));
+        return refused == 13 ? 0 : 3;
     }
     if (argc > 1 && strcmp(argv[1], "--factor") == 0) {
         /* node states: the rest state at every node; ctrl = one row per node, the factor fl*fv + fp of the interval */
@@ -105,6 +115,30 @@ int main(int argc, char **argv) {
         }
         for (int k = 0; k < 3; ++k) for (int j = 0; j < 5; ++j) printf("%.17g\n", Phi[k][j]);
         for (int k = 0; k < 3; ++k) for (int j = 0; j < 5; ++j) printf("%.17g\n", J[k][j][5]);
+        return 0;
+    }
+    if (argc > 1 && strcmp(argv[1], "--hess") == 0) {
+        /* second derivatives of the three interval maps at the rest state, contracted with multipliers of one: 15 pairs each */
+        double X[4][5], lam[3][5], H[3][15];
+        FesHessBuffers hb;
+        for (int k = 0; k < 4; ++k) memcpy(X[k], x0, sizeof(x0));
+        for (int k = 0; k < 3; ++k) for (int j = 0; j < 5; ++j) { lam[k][j] = 1.0; X[k][0] = 0.2; X[k][1] = 30.0 + 10.0 * k; }
+        memset(&hb, 0, sizeof(hb));
+        hb.params = params;
+        hb.X = X;
+        hb.stim_win = &win[0][0];
+        hb.multipliers = lam;
+        hb.H = H;
+        d.dirs = FES_DIR_X0 | FES_DIR_U;
+        d.trace_every = 0;
+        d.trace_batch = 0;
+        if (fes_shoot_hess_num_dirs(d.model_kind, d.fatigue, d.n_trunc, d.dirs) != 5) return 4;
+        int rch = fes_shoot_hess_host_f64(&d, &hb, NULL);
+        if (rch != 0) {
+            fprintf(stderr, "fes_shoot_hess_host_f64 -> %d (%s)\n", rch, fes_strerror(rch));
+            return 10;
+        }
+        for (int k = 0; k < 3; ++k) for (int p = 0; p < 15; ++p) printf("%.17g\n", H[k][p]);
         return 0;
     }
     int rc = fes_ivp_host_f64(&d, &b, NULL);

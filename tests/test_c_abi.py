@@ -30,7 +30,7 @@ def test_library_is_self_contained_and_refuses_bad_arguments(client):
     assert "torch" not in deps and "python" not in deps.lower()
     r = subprocess.run([client, "--errors"], capture_output=True, text=True)
     assert r.returncode == 0, r.stdout + r.stderr
-    assert "refused 12 of 12" in r.stdout
+    assert "refused 13 of 13" in r.stdout
 
 
 @pytest.mark.skipif(torch.cuda.is_available(), reason="checks the behaviour WITHOUT a device")
@@ -65,3 +65,24 @@ def test_plain_c_call_with_force_factor_matches_the_python_surface(client):
                     force_factor=torch.tensor([1.0, 0.8, 1.15], dtype=torch.float64, device=dev))
     assert np.array_equal(vals[0], res.Phi[:, :, 0].cpu().numpy())
     assert np.array_equal(vals[1], res.Jc[:, :, 0].cpu().numpy())
+
+
+@pytest.mark.gpu
+def test_plain_c_call_of_the_second_order_entry_point_matches_the_python_surface(client):
+    """fes_shoot_hess_host_f64 from C: the contracted blocks are those of fes.shoot_hessian(multipliers=1)."""
+    from cocofest_b200 import fes
+
+    r = subprocess.run([client, "--hess"], capture_output=True, text=True)
+    assert r.returncode == 0, r.stderr
+    vals = np.array([float(x) for x in r.stdout.split()]).reshape(3, 15)
+    dev = torch.device("cuda", 0)
+    pad = float(fes.PAD_TIME)
+    win = torch.tensor([[pad, pad, 0.0], [pad, 0.0, 0.1], [0.0, 0.1, 0.2]], dtype=torch.float64, device=dev)
+    p = torch.tensor(fes.default_params(fes.FES_DING2003), device=dev)
+    X = torch.tensor([0, 0, 3009, 0.050957, 0.103], dtype=torch.float64, device=dev)[None, :, None].repeat(4, 1, 1).contiguous()
+    X[:3, 0, 0] = 0.2
+    X[:3, 1, 0] = torch.tensor([30.0, 40.0, 50.0], dtype=torch.float64, device=dev)
+    lam = torch.ones((3, 5, 1), dtype=torch.float64, device=dev)
+    res = fes.shoot_hessian(fes.FES_DING2003, True, p, X, win, 0.3 / 3, n_steps=10, multipliers=lam, second=False)
+    assert np.array_equal(vals, res.H[:, :, 0].cpu().numpy())
+    assert np.abs(vals).max() > 0

@@ -202,3 +202,30 @@ def test_argument_checks_through_the_c_abi(backend):
     assert L.fes_shoot_hess_num_dirs(_lib.FES_HMED2018, 1, 10, fes.FES_DIR_X0 | fes.FES_DIR_U | fes.FES_DIR_C) == 16
     if backend.type == "cuda":
         torch.cuda.synchronize()
+
+
+@pytest.mark.parametrize("backend", BACKENDS, indirect=True)
+def test_edge_shapes_single_unit_long_and_per_scenario_windows(backend):
+    """One scenario / one step / one-slot window; a window left-padded to 300 slots (the truncation sweep's layout) gives the
+    numbers of the short one bit for bit (pads add exact zeros); a per-scenario window equals the shared one."""
+    kind, fat = fes.FES_DING2003, True
+    par = torch.tensor(cf.ModelMaker.create_model("ding2003_with_fatigue", stim_time=[0.0], sum_stim_truncation=1).param_vector(), device=backend)
+    X = torch.tensor([[[0.3], [40.0], [2800.0], [0.055], [0.11]]] * 2, dtype=torch.float64, device=backend)     # [2, 5, 1]
+    win1 = torch.tensor([[0.0]], dtype=torch.float64, device=backend)
+    one = fes.shoot_hessian(kind, fat, par, X, win1, 0.05, n_steps=1)
+    assert tuple(one.D2.shape) == (1, 5, 15, 1) and bool(torch.isfinite(one.D2).all())
+    ten = fes.shoot_hessian(kind, fat, par, X, win1, 0.05, n_steps=10)
+    assert float((one.D2 - ten.D2).abs().max()) > 0.0               # the discrete map, not the continuous one
+    short = torch.tensor([[-0.1, -0.05, 0.0]], dtype=torch.float64, device=backend)
+    long = torch.cat([torch.full((1, 297), -1.0e7, dtype=torch.float64, device=backend), short], dim=1)
+    a = fes.shoot_hessian(kind, fat, par, X, short, 0.05, n_steps=4).D2
+    b = fes.shoot_hessian(kind, fat, par, X, long, 0.05, n_steps=4).D2
+    assert torch.equal(a, b)
+    B = 4
+    XB = X.repeat(1, 1, B) * torch.linspace(0.9, 1.1, B, dtype=torch.float64, device=backend)
+    shared = fes.shoot_hessian(kind, fat, par, XB, short, 0.05, n_steps=4).D2
+    per = fes.shoot_hessian(kind, fat, par[:, None].repeat(1, B), XB, short[:, :, None].repeat(1, 1, B), 0.05, n_steps=4).D2
+    assert torch.equal(shared, per)
+    # pads only: no pulse has happened, the Cn row is pure decay and the blocks stay finite
+    pads = torch.full((1, 3), -1.0e7, dtype=torch.float64, device=backend)
+    assert bool(torch.isfinite(fes.shoot_hessian(kind, fat, par, X, pads, 0.05, n_steps=4).D2).all())
