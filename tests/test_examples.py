@@ -54,3 +54,10 @@ def test_force_factor_example_runs():
     r = _run("dynamics", "force_length_velocity_factor.py", args=("--scenarios", "4096"))
     assert r.returncode == 0, r.stderr[-2000:]
     assert "with    relationships" in r.stdout and "through Jc" in r.stdout
+
+
+@pytest.mark.gpu
+def test_node_shooting_comparison_example_runs():
+    r = _run("sensitivity", "node_shooting_comparison.py", args=("--starts", "1024"))
+    assert r.returncode == 0, r.stderr[-2000:]
+    assert "observed order of RK4" in r.stdout and "errors agree within a factor" in r.stdout
