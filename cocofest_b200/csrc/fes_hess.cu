@@ -9,7 +9,7 @@ static int launch_hess_one(const HessArgs &a, cudaStream_t s) {
     const int64_t total = (int64_t)a.ns * a.npairs * a.B;
     // 148 SMs x 16 resident blocks of 128 threads cover the device; larger problems stride over the grid
     const int64_t blocks = std::min<int64_t>((total + 127) / 128, (int64_t)148 * 16 * 8);
-    fes_hess_kernel<KIND, FAT, FC><<<(unsigned)blocks, 128, 0, s>>>(a);
+    fes_hess_kernel<KIND, FAT, FC><<<(unsigned)blocks, 128, (size_t)(2 * a.S + 1) * sizeof(double), s>>>(a);
     return (int)cudaGetLastError();
 }
 

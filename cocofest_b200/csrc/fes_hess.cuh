@@ -12,7 +12,8 @@
 // arithmetic -- numbers (v, a, b, c) with a = d/dz_i, b = d/dz_j, c = d2/dz_i dz_j, closed under + - * 1/x exp tanh -- so
 // the `c` parts of the end state ARE the wanted entries (forward-over-forward differentiation of the same RK stages as
 // external/bioptim/bioptim/dynamics/integrator.py:300-365).  No workspace and no tables: the window sum
-// S(t) = E_k eps(t - t_k) is assembled per thread (2 N exp per interval), eps at the stage offsets is three exp per step.
+// S(t) = E_k eps(t - t_k) is assembled per thread (2 N exp per interval), eps at the stage offsets is a table of 2 S + 1
+// doubles that every block builds in shared memory (the same numbers as fes_core.cuh's stage table).
 // The unit is small (20 doubles of state) and the grid is nz (nz + 1) / 2 times larger than the interval kernel's, which
 // is what a small NMPC batch wants.  fp64 only.
 #pragma once
@@ -86,7 +87,7 @@ FES_HD void hess_pair_of(int p, int nz, int &i, int &j) {
 // One (interval k, pair (pi, pj), scenario b): writes d2 Phi_k[r] / dz_pi dz_pj for r = 0..NX-1 into out[r].
 // z = (Cn, F [, A, Tau1, Km], controls of the model [, force factor]).
 template <int KIND, bool FAT, bool FC>
-FES_HD void hess_unit(const HessArgs &a, int k, int pi, int pj, int64_t b, double *out) {
+FES_HD void hess_unit(const HessArgs &a, const double *eps, int k, int pi, int pj, int64_t b, double *out) {
     constexpr int NX = FAT ? 5 : 2;
     auto par = [&](int j) { return a.params[j * a.pB + b * a.pS]; };
     auto seed = [&](double v, int idx) { return HD{v, idx == pi ? 1.0 : 0.0, idx == pj ? 1.0 : 0.0, 0.0}; };
@@ -164,10 +165,10 @@ FES_HD void hess_unit(const HessArgs &a, int k, int pi, int pj, int64_t b, doubl
     };
 
     // One loop per scheme, so that a step is straight-line code.  RK4: x, the running combination, the stage state and ONE
-    // stage derivative are live (not k1..k4): 80 doubles.  eps at the stage offsets is fes_core.cuh's stage table, evaluated
-    // here (two exp per step, the end of a step is the start of the next).
+    // stage derivative are live (not k1..k4): 80 doubles.  eps[j] = exp(-(j h/2)/tauc), j = 0..2S, is fes_core.cuh's stage
+    // table (hess_eps_table): the same for every unit of a call, built once per block in shared memory by the kernel.
     const double h = a.h;
-    auto eps_at = [&](int idx) { return exp(-(0.5 * h * (double)idx) * inv_tauc); };
+    auto eps_at = [&](int idx) { return eps[idx]; };
     if (a.scheme == 4) {
         double e0 = 1.0;
         for (int s = 0; s < a.S; ++s) {
@@ -219,13 +220,15 @@ FES_HD void hess_unit(const HessArgs &a, int k, int pi, int pj, int64_t b, doubl
     for (int r = 0; r < NX; ++r) out[r] = x[r].c;
 }
 
+FES_HD double hess_eps_entry(const HessArgs &a, int idx) { return exp(-(0.5 * a.h * (double)idx) / a.tauc); }
+
 template <int KIND, bool FAT, bool FC>
-FES_HD void hess_store(const HessArgs &a, int k, int p, int64_t b) {
+FES_HD void hess_store(const HessArgs &a, const double *eps, int k, int p, int64_t b) {
     constexpr int NX = FAT ? 5 : 2;
     int pi, pj;
     hess_pair_of(p, a.nz, pi, pj);
     double o[NX];
-    hess_unit<KIND, FAT, FC>(a, k, pi, pj, b, o);
+    hess_unit<KIND, FAT, FC>(a, eps, k, pi, pj, b, o);
     if (a.D2) {
 #pragma unroll
         for (int r = 0; r < NX; ++r) a.D2[(((int64_t)k * NX + r) * a.npairs + p) * a.B + b] = o[r];
@@ -244,11 +247,14 @@ FES_HD void hess_store(const HessArgs &a, int k, int p, int64_t b) {
 #endif
 template <int KIND, bool FAT, bool FC>
 __global__ void __launch_bounds__(128, FES_HESS_MIN_BLOCKS) fes_hess_kernel(const HessArgs a) {
+    extern __shared__ double s_eps[];   // 2 S + 1 doubles (dynamic)
+    for (int j = threadIdx.x; j <= 2 * a.S; j += blockDim.x) s_eps[j] = hess_eps_entry(a, j);
+    __syncthreads();
     const int64_t total = (int64_t)a.ns * a.npairs * a.B;
     for (int64_t idx = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; idx < total; idx += (int64_t)gridDim.x * blockDim.x) {
         const int64_t b = idx % a.B, rest = idx / a.B;
         const int p = (int)(rest % a.npairs), k = (int)(rest / a.npairs);
-        hess_store<KIND, FAT, FC>(a, k, p, b);
+        hess_store<KIND, FAT, FC>(a, s_eps, k, p, b);
     }
 }
 

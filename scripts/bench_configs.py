@@ -303,12 +303,19 @@ def run_configs(wanted, dev, dtype="f64", steps=3, warmup=3, scale=1.0, flush=No
                     r = plan_fd(X, U)
                 return r
             _, ms_fd = timed(fd_route, steps, warmup, flush)
-            add("5h: the same horizon, exact Hessian blocks sum_r lambda_r d2Phi_r/dz dz (21 pairs per interval) in one launch: second-order tangents, one thread per (scenario, interval, pair)",
-                "fes_hess_kernel<DING2007, fatigue, X0|U> (no static count: the step is not one basic block)", B * ns * S, ms,
-                out.H.numel() * 8, (X.numel() + U.numel() + lam.numel()) * 8, dtype,
-                {"scenarios": B, "n_shooting": ns, "pairs": out.H.shape[1], "pair_steps_per_s": B * ns * S * out.H.shape[1] / (statistics.mean(ms) * 1e-3),
+            # static counts of the hyper-dual step are per (pair, step): scaled to the config's unit (one RK4 step of an interval with
+            # all its pairs) so that the issue fraction reads like the other records'
+            kname, pairs = "fes_hess_kernel<DING2007, fatigue, X0|U>", out.H.shape[1]
+            c2 = None
+            if counts and kname in counts:
+                c2 = {kname: {**counts[kname], **{f: counts[kname][f] * pairs for f in ("fp64_inst", "fp64_flop", "fp32_inst", "fp32_flop")}}}
+            recs.append(record(
+                "5h: the same horizon, exact Hessian blocks sum_r lambda_r d2Phi_r/dz dz (21 pairs per interval) in one launch: second-order tangents, one thread per (scenario, interval, pair)",
+                kname, B * ns * S, ms, out.H.numel() * 8, (X.numel() + U.numel() + lam.numel()) * 8, dtype, c2, peaks, hbm_peak,
+                {"scenarios": B, "n_shooting": ns, "pairs": pairs, "pair_steps_per_s": B * ns * S * pairs / (statistics.mean(ms) * 1e-3),
+                 "counts_note": "inst_per_trajectory_step = 21 pairs x the per-pair RK4 step of the shipped SASS",
                  "finite_difference_route_ms": statistics.mean(ms_fd),
-                 "finite_difference_route": "12 ShootPlan calls (central differences of the exact Jacobian, ~1e-10), arithmetic of the differences not included"})
+                 "finite_difference_route": "12 ShootPlan calls (central differences of the exact Jacobian, ~1e-10), arithmetic of the differences not included"}))
         if "5pf" in wanted:
             # the dense parameter columns of a fatigue model (what a fatigue-parameter identification would differentiate)
             fn = lambda: fes.shoot(fes.FES_DING2007, True, p, X, win, proto["dt"], n_steps=S, ctrl=U, want=("p", "pf"),

@@ -85,7 +85,8 @@ def main():
         # every RK4 step holds exactly four reciprocals (one per stage, fes_core.cuh nominal_rhs): a path with 8 of them
         # is two steps unrolled by the compiler (the small no-sensitivity kernels) -- counts below are PER STEP
         rcp = sum(v for k, v in mix.items() if k.startswith("MUFU.RCP"))
-        steps = max(1, rcp // 4)
+        # (the second-order kernel keeps the two reciprocals of F' apart: eight per step, fes_hess.cuh)
+        steps = max(1, rcp // (8 if "fes_hess_kernel" in sym else 4))
         if steps > 1:
             mix = Counter({k: v // steps for k, v in mix.items()})
         fp64 = mix["DFMA"] + mix["DMUL"] + mix["DADD"]

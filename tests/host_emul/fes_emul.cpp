@@ -276,11 +276,14 @@ int ident_host(const FesDesc *d, const FesIdentBuffers *b, const FesIdentOptions
 // second-order tangents: the same hess_unit template, plain loops over (interval, pair, scenario)
 template <int KIND, bool FAT>
 static void hess_cpu_kf(const HessArgs &a) {
+    std::vector<double> eps_v(2 * a.S + 1);
+    for (int j = 0; j <= 2 * a.S; ++j) eps_v[j] = hess_eps_entry(a, j);
+    const double *eps = eps_v.data();
     for (int k = 0; k < a.ns; ++k)
         for (int p = 0; p < a.npairs; ++p)
             for (int64_t b = 0; b < a.B; ++b) {
-                if (a.factor) hess_store<KIND, FAT, true>(a, k, p, b);
-                else hess_store<KIND, FAT, false>(a, k, p, b);
+                if (a.factor) hess_store<KIND, FAT, true>(a, eps, k, p, b);
+                else hess_store<KIND, FAT, false>(a, eps, k, p, b);
             }
 }
 
