@@ -62,6 +62,11 @@ def _worker(rank, world, port, out_dir):
         shoot = lambda p, x, f: fes.shoot(fes.FES_DING2003, True, p, x, winN, proto["dt"], n_steps=10, force_factor=f)
         sh = shoot(sharding.shard_last(params, rank, world), sharding.shard_last(X, rank, world), sharding.shard_last(fc, rank, world))
         G, Jx, Jc = (sharding.gather_last(t.contiguous(), batch=B) for t in (sh.G, sh.Jx, sh.Jc))
+        # ... and the second-order blocks of the same scenarios (fes_shoot_hess_f64: the batch is the last axis there too)
+        lam = torch.rand((ns, 5, B), generator=torch.Generator().manual_seed(2), dtype=torch.float64)
+        hess = lambda p, x, f, l: fes.shoot_hessian(fes.FES_DING2003, True, p, x, winN, proto["dt"], n_steps=10, force_factor=f, multipliers=l)
+        hs = hess(*(sharding.shard_last(t, rank, world) for t in (params, X, fc, lam)))
+        D2, H = sharding.gather_last(hs.D2, batch=B), sharding.gather_last(hs.H, batch=B)
         proto_h, cand, x0_h, ctrl_h = protocols.hmed2018_candidates(B)
         win_h = torch.tensor(proto_h["win"])
         truth = torch.tensor(fes.default_params(fes.FES_HMED2018))
@@ -75,6 +80,8 @@ def _worker(rank, world, port, out_dir):
             assert torch.equal(full_x, ref.x_final) and torch.equal(full_s, ref.sens_final)
             rs = shoot(params, X, fc)
             assert torch.equal(G, rs.G) and torch.equal(Jx, rs.Jx) and torch.equal(Jc, rs.Jc)
+            rh = hess(params, X, fc, lam)
+            assert torch.equal(D2, rh.D2) and torch.equal(H, rh.H) and D2.shape == (ns, 5, 21, B)
             ri = ident(cand)
             assert torch.equal(P, ri.params) and torch.equal(C, ri.cost)
             open(os.path.join(out_dir, "ok"), "w").write("ok")
