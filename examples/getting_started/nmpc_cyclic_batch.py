@@ -7,7 +7,7 @@ the solved horizon is shifted (fes_nmpc.py:44-85).  The solver stays on the host
 script shows is everything the solver CONSUMES per iteration, for 16 384 scenarios in one call:
 
     defects g_k = x_{k+1} - Phi_k(x_k, u_k),  dPhi_k/dx_k,  dPhi_k/du_k          fes.ShootPlan (one call per iteration)
-    second derivatives for an exact-Hessian solver                                FesShooting.second_derivatives
+    exact Hessian blocks sum_r lambda_r d2Phi_r/dz dz of the continuity rows          FesShooting.hessian (one launch per iteration)
     window carry-over and warm-start shift between cycles                         FesNmpcBatch.update_stim / .advance
 
 and checks the one property that needs no solver: node states produced by integrating a control sequence are defect-free.
@@ -55,10 +55,20 @@ for cycle in range(args.cycles):
     torch.cuda.synchronize()
     per_iter = (time.perf_counter() - t0) / 20
     worst = float((res.G.abs() / X[1:].abs().amax(dim=(0, 2), keepdim=True)).max())
+    # what Ipopt's default (exact Hessian, ipopt_options.py:88) adds per iteration: the blocks of the Lagrangian Hessian of the
+    # continuity rows for the current multipliers, from the second-order tangent kernel; the full tensor for a few scenarios
+    lam = torch.randn((ns, 5, B), generator=gen, dtype=torch.float64).to(dev)
+    torch.cuda.synchronize()
+    t0 = time.perf_counter()
+    hes = shooting.hessian(X, pulse_width, multipliers=lam, second=False)
+    torch.cuda.synchronize()
+    t_hes = time.perf_counter() - t0
     D2 = shooting.second_derivatives(X[:, :, :256].contiguous(), pulse_width[:, :, :256].contiguous())
+    Hd = torch.einsum("krb,krijb->kijb", lam[:, :, :256], D2)
+    assert float((hes.full(hes.H)[..., :256] - Hd).abs().max()) <= 1e-12 * float(Hd.abs().max())
     print(f"cycle {cycle}: {B} scenarios x {ns} intervals, defects + dPhi/dx + dPhi/dpw in {1e3 * per_iter:.3f} ms per iteration "
           f"({B * ns / per_iter:.3g} interval integrations/s); largest relative defect of the integrated nodes {worst:.1e}; "
-          f"second derivatives of 256 scenarios: {tuple(D2.shape)}")
+          f"exact Hessian blocks {tuple(hes.H.shape)} in {1e3 * t_hes:.2f} ms; second derivatives of 256 scenarios: {tuple(D2.shape)}")
     assert worst < 1e-12
     # next cycle: carry the pulses over, shift the solved horizon, start from where this one ended
     nmpc.update_stim()
