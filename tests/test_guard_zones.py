@@ -149,3 +149,28 @@ def test_shoot_with_force_factor_stays_inside_its_buffers(monkeypatch, name):
         torch.cuda.synchronize()
     arena.check()
     assert all(same(a, b) for a, b in ((got.G, plain.G), (got.Phi, plain.Phi), (got.Jx, plain.Jx), (got.Ju, plain.Ju), (got.Jc, plain.Jc)))
+
+
+@pytest.mark.parametrize("name", list(MODELS))
+def test_second_order_kernel_stays_inside_its_buffers(monkeypatch, name):
+    """fes_shoot_hess_f64: D2 and H between guard zones, every input between NaN pads, with and without the force factor;
+    B = 70 leaves a partial last block, per-scenario and shared windows / controls."""
+    dev = torch.device("cuda", 0)
+    for kw, factor in ((dict(B=70, N=6, ns=5, shared_ctrl=True), False), (dict(B=33, N=4, ns=3, per_traj_win=True, shared_ctrl=False), True)):
+        pb = random_problem(name, seed=3, **kw)
+        params, x0, win, ctrl = to_lib(pb, dev)
+        B, ns, nx = x0.shape[-1], pb["ns"], x0.shape[0]
+        X = (x0[None] * torch.linspace(1.0, 0.9, ns + 1, dtype=torch.float64, device=dev)[:, None, None]).contiguous()
+        X[:, 0] += 0.2
+        X[:, 1] += 30.0
+        lam = torch.rand((ns, nx, B), dtype=torch.float64, device=dev)
+        ff = (0.7 + 0.5 * torch.rand((ns, B), dtype=torch.float64, device=dev)) if factor else None
+        call = lambda p, x, w, c, l, f: fes.shoot_hessian(pb["kind"], pb["fat"], p, x, w, pb["dt"], n_steps=3, ctrl=c, multipliers=l, force_factor=f)
+        plain = call(params, X, win, ctrl, lam, ff)
+        arena = Arena()
+        with monkeypatch.context() as mp:
+            mp.setattr(fes, "_empty", arena)
+            got = call(padded(params), padded(X), padded(win), padded(ctrl), padded(lam), padded(ff))
+            torch.cuda.synchronize()
+        arena.check()
+        assert same(got.D2, plain.D2) and same(got.H, plain.H) and bool(torch.isfinite(plain.D2).all())
