@@ -91,3 +91,24 @@ def test_identify_host_equals_device():
     h = fes.identify(fes.FES_HMED2018, hp, hw, proto["dt"], ht, ctrl=hc, max_iter=3)
     for a, b in ((h.params, d.params), (h.cost, d.cost), (h.grad, d.grad), (h.hess, d.hess), (h.evaluations, d.evaluations)):
         assert torch.equal(a, b.cpu())
+
+
+@pytest.mark.parametrize("name", ["ding2007_with_fatigue", "hmed2018"])
+def test_second_order_host_equals_device(name):
+    """fes_shoot_hess_host_f64 (CPU tensors in and out) against fes_shoot_hess_f64 on device tensors: bit-identical, with the
+    phase record of the host path."""
+    dev = torch.device("cuda", 0)
+    pb = random_problem(name, B=300, N=5, ns=6, seed=6, shared_ctrl=False)
+    params, x0, win, ctrl = to_lib(pb, dev)
+    ns, nx, B = pb["ns"], x0.shape[0], x0.shape[-1]
+    X = (x0[None] * torch.linspace(1.0, 0.9, ns + 1, dtype=torch.float64, device=dev)[:, None, None]).contiguous()
+    X[:, 0] += 0.1
+    X[:, 1] += 20.0
+    lam = torch.rand((ns, nx, B), dtype=torch.float64, device=dev)
+    d = fes.shoot_hessian(pb["kind"], pb["fat"], params, X, win, pb["dt"], n_steps=4, ctrl=ctrl, multipliers=lam)
+    hp, hX, hw, hc, hl = _cpu(params, X, win, ctrl, lam)
+    h = fes.shoot_hessian(pb["kind"], pb["fat"], hp, hX, hw, pb["dt"], n_steps=4, ctrl=hc, multipliers=hl)
+    assert h.D2.device.type == "cpu" and h.H.is_pinned()
+    assert torch.equal(h.D2, d.D2.cpu()) and torch.equal(h.H, d.H.cpu())
+    t = fes.last_host_timing()
+    assert t["kernels_ms"] > 0 and t["h2d_ms"] > 0 and t["d2h_ms"] > 0
