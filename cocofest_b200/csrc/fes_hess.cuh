@@ -14,8 +14,9 @@
 // external/bioptim/bioptim/dynamics/integrator.py:300-365).  No workspace and no tables: the window sum
 // S(t) = E_k eps(t - t_k) is assembled per thread (2 N exp per interval), eps at the stage offsets is a table of 2 S + 1
 // doubles that every block builds in shared memory (the same numbers as fes_core.cuh's stage table).
-// The unit is small (20 doubles of state) and the grid is nz (nz + 1) / 2 times larger than the interval kernel's, which
-// is what a small NMPC batch wants.  fp64 only.
+// The unit is small (20 doubles of state per stage vector) and the grid is nz (nz + 1) / 2 times the interval kernel's.
+// Cost: each pair recomputes value and first-order parts, so the call costs ~3.7 x the difference
+// quotients of the exact Jacobian (12 interval-kernel calls); what it buys is rounding-level accuracy.  fp64 only.
 #pragma once
 
 #include "fes_core.cuh"
