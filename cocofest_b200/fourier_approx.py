@@ -42,6 +42,21 @@ class FourierSeries:
         return ab[0, 0] / 2.0 + np.sum(a * np.cos(w) + b * np.sin(w), axis=0)
 
 
+    def fourier_approx(self, x, y, n, show=False):
+        """The approximation of the samples by their first ``n`` harmonics, evaluated at ``x`` (fourier_approx.py:40-49).  The
+        reference also draws both curves with matplotlib; plotting is outside this path, so that part is opt-in (``show=True``)
+        and needs matplotlib."""
+        ab = self.compute_real_fourier_coeffs(x, y, n)
+        y_approx = self.fit_func_by_fourier_series_with_real_coeffs(x, ab)
+        if show:
+            import matplotlib.pyplot as plt
+
+            plt.scatter(x, y, color="blue", s=5, marker=".")
+            plt.plot(x, y_approx, color="red", linewidth=1)
+            plt.show()
+        return y_approx
+
+
 def force_to_track(force_tracking, n_shooting, n_harmonics=50):
     """fes_ocp.py:539-548: the target force at the ns+1 nodes from ``force_tracking = [time, force]``."""
     fs = FourierSeries()

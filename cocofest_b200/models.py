@@ -225,6 +225,48 @@ class DingModelFrequency(FesModel):
         return np.array([cn_dot, f_dot, self.a_dot_fun(a, f), self.tau1_dot_fun(tau1, f), self.km_dot_fun(km, f)])
 
 
+    # -- bioptim hooks (ding2003.py:313-392 and the same block of every model) -----------------------------------------
+    @staticmethod
+    def dynamics(time, states, controls, parameters, algebraic_states, numerical_timeseries, nlp=None, fes_model=None,
+                 force_length_relationship=1, force_velocity_relationship=1, passive_force_relationship=0):
+        """The reference's ``dyn_func``: dx/dt of the phase model at one point, states ordered Cn, F (, A, Tau1, Km), the
+        controls of the model (last pulse width | the window's pulse intensities) and the window's pulse times as
+        ``numerical_timeseries``.  Here it evaluates ``system_dynamics`` on numbers (no casadi graph) and returns a
+        ``DynamicsEvaluation(dxdt, defects)`` record like bioptim's; ``parameters`` / ``algebraic_states`` are unused, as in the
+        reference."""
+        model = fes_model if fes_model is not None else nlp.model
+        x = [float(v) for v in np.asarray(states, dtype=float).reshape(-1)]
+        u = [] if controls is None else [float(v) for v in np.asarray(controls, dtype=float).reshape(-1)]
+        kw = dict(cn=x[0], f=x[1], t=float(np.asarray(time, dtype=float).reshape(-1)[0]),
+                  t_stim_prev=[float(v) for v in np.asarray(numerical_timeseries, dtype=float).reshape(-1)],
+                  force_length_relationship=force_length_relationship, force_velocity_relationship=force_velocity_relationship,
+                  passive_force_relationship=passive_force_relationship)
+        if model._with_fatigue:
+            kw.update(a=x[2], tau1=x[3], km=x[4])
+        if model.kind == FES_DING2007:
+            kw["pulse_width"] = u[0]
+        elif model.kind == FES_HMED2018:
+            kw["pulse_intensity"] = u
+        return DynamicsEvaluation(dxdt=model.system_dynamics(**kw), defects=None)
+
+    def declare_ding_variables(self, ocp, nlp, numerical_data_timeseries=None):
+        """bioptim's state / control declaration (``StateConfigure`` + ``ConfigureProblem.configure_dynamics_function``) builds
+        the casadi NLP, which is the control plane around this path and stays with bioptim: where bioptim
+        is installed the reference's own model classes declare the variables and ``cocofest_b200.GpuRK4`` integrates them."""
+        raise NotImplementedError(
+            "declare_ding_variables assembles bioptim's casadi NLP, which is outside the accelerated path: configure the problem "
+            "with the reference's model classes and pass ode_solver=cocofest_b200.GpuRK4(...) (INTEGRATION.md section 3), or "
+            "evaluate defects / Jacobians / Hessian blocks directly with cocofest_b200.FesShooting")
+
+
+class DynamicsEvaluation:
+    """The record bioptim's dynamics functions return (``bioptim.DynamicsEvaluation``): ``dxdt`` and ``defects``."""
+
+    def __init__(self, dxdt=None, defects=None):
+        self.dxdt = dxdt
+        self.defects = defects
+
+
 class _FatigueMixin:
     """Fatigue states A, Tau1, Km (reference: ding2003_with_fatigue.py:50-59, 197-240)."""
 
@@ -311,6 +353,16 @@ class DingModelPulseWidthFrequency(DingModelFrequency):
     def a_calculation(self, a_scale, pulse_width):
         return a_scale * (1 - math.exp(-(pulse_width - self.pd0) / self.pdt))
 
+    @staticmethod
+    def a_calculation_identification(a_scale, pulse_width, pd0, pdt):
+        """``a_calculation`` with pd0 / pdt passed in (the identification OCP's parameters, ding2007.py:190-212; used by
+        ``custom_constraints.py:93``)."""
+        return a_scale * (1 - math.exp(-(pulse_width - pd0) / pdt))
+
+    def set_impulse_width(self, value):
+        """Parameter callback of the pulse-width OCPs (ding2007.py:215-225): the optimised widths become the model's."""
+        self.pulse_width = value
+
     def _a_input(self, a, pulse_width=None, **kw):
         return self.a_calculation(a, pulse_width)
 
@@ -367,6 +419,15 @@ class DingModelPulseIntensityFrequency(DingModelFrequency):
 
     def lambda_i_calculation(self, pulse_intensity):
         return self.ar * (math.tanh(self.bs * (pulse_intensity - self.Is)) + self.cr)
+
+    @staticmethod
+    def lambda_i_calculation_identification(pulse_intensity, ar, bs, Is, cr):
+        """``lambda_i_calculation`` with the recruitment parameters passed in (hmed2018.py:183-204; ``custom_constraints.py:41``)."""
+        return ar * (math.tanh(bs * (pulse_intensity - Is)) + cr)
+
+    def set_impulse_intensity(self, value):
+        """Parameter callback of the pulse-intensity OCPs (hmed2018.py:206-218): one entry per pulse."""
+        self.impulse_intensity = [value[i] for i in range(np.shape(value)[0])]
 
     def get_lambda_i(self, nb_stim: int, pulse_intensity) -> list:
         return [self.lambda_i_calculation(pulse_intensity[i]) for i in range(nb_stim)]

@@ -98,6 +98,53 @@ def test_scalar_helpers_match_reference_component_pins():
             np.testing.assert_allclose(m.system_dynamics(**kw), pt["xdot"], rtol=1e-13, atol=1e-13)
 
 
+# every method name the reference's model classes define (cocofest/models/{fes_model,ding2003*,ding2007*,hmed2018*}.py)
+REFERENCE_MODEL_METHODS = {
+    "ding2003": ["set_a_rest", "set_km_rest", "set_tau1_rest", "set_tau2", "standard_rest_values", "serialize", "get_r0", "get_lambda_i",
+                 "system_dynamics", "exp_time_fun", "ri_fun", "cn_sum_fun", "cn_dot_fun", "f_dot_fun", "calculate_cn_dot", "dynamics",
+                 "declare_ding_variables", "get_numerical_data_time_series"],
+    "ding2003_with_fatigue": ["set_alpha_a", "set_alpha_tau1", "set_alpha_km", "set_tau_fat", "a_dot_fun", "tau1_dot_fun", "km_dot_fun"],
+    "ding2007": ["set_a_scale", "set_pd0", "set_pdt", "a_calculation", "a_calculation_identification", "set_impulse_width"],
+    "hmed2018": ["set_ar", "set_bs", "set_Is", "set_cr", "lambda_i_calculation", "lambda_i_calculation_identification",
+                 "set_impulse_intensity", "min_pulse_intensity"],
+}
+
+
+def test_every_method_of_the_reference_models_exists():
+    for name, methods in REFERENCE_MODEL_METHODS.items():
+        m = cf.ModelMaker.create_model(name, stim_time=[0.0, 0.1], sum_stim_truncation=3)
+        missing = [fn for fn in methods if not callable(getattr(m, fn, None))]
+        assert not missing, (name, missing)
+
+
+def test_identification_helpers_and_the_dynamics_hook():
+    """a_calculation_identification / lambda_i_calculation_identification (custom_constraints.py:41, :93) are the model's own
+    expressions with the parameters passed in; the pin 0.0799499 is the reference's
+    (tests/shard1/test_models_dynamics_without_bioptim.py:249).  ``dynamics`` is the reference's dyn_func on numbers."""
+    m7 = cf.ModelMaker.create_model("ding2007_with_fatigue", stim_time=[0.0, 0.1], sum_stim_truncation=3)
+    assert m7.a_calculation_identification(4920, 3e-4, m7.pd0, m7.pdt) == m7.a_calculation(4920, 3e-4)
+    m7.set_impulse_width([2e-4, 3e-4])
+    assert m7.pulse_width == [2e-4, 3e-4]
+    mh = cf.ModelMaker.create_model("hmed2018", stim_time=[0.0, 0.1], sum_stim_truncation=3)
+    np.testing.assert_almost_equal(mh.lambda_i_calculation(30), 0.0799499)
+    assert mh.lambda_i_calculation_identification(30, mh.ar, mh.bs, mh.Is, mh.cr) == mh.lambda_i_calculation(30)
+    mh.set_impulse_intensity(np.array([40.0, 55.0]))
+    assert mh.impulse_intensity == [40.0, 55.0]
+    fixtures = json.loads((Path(__file__).parent / "golden" / "reference_rhs.json").read_text())["models"]
+    for name, fx in fixtures.items():
+        prev = {"time": list(fx["previous_stim"]["time"])}
+        if "pulse_intensity" in fx["previous_stim"]:
+            prev["pulse_intensity"] = list(fx["previous_stim"]["pulse_intensity"])
+        m = cf.ModelMaker.create_model(name, stim_time=fx["stim_time"], previous_stim=prev, sum_stim_truncation=fx["sum_stim_truncation"])
+        for pt in fx["points"]:
+            ev = type(m).dynamics(pt["t"], np.array(pt["x"]), np.array(pt["u"]) if pt.get("u") else None, None, None,
+                                  np.array(fx["window"][pt["node"]]), nlp=None, fes_model=m)
+            np.testing.assert_allclose(ev.dxdt, pt["xdot"], rtol=1e-13, atol=1e-13)
+            assert ev.defects is None
+        with pytest.raises(NotImplementedError, match="GpuRK4"):
+            m.declare_ding_variables(None, None)
+
+
 def test_prepare_n_shooting():
     assert cf.OcpFes.prepare_n_shooting([0, 0.1, 0.2], 0.3) == 3
     assert cf.OcpFes.prepare_n_shooting([0, 0.005, 0.1, 0.105, 0.2, 0.205], 0.3) == 60

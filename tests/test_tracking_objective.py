@@ -25,6 +25,8 @@ def test_fourier_fit_matches_reference_class(case):
     if case["n"] == 50:
         np.testing.assert_allclose(force_to_track([x, y], case["n_shooting"]), np.array(case["force_to_track"]),
                                    rtol=1e-12, atol=1e-10)
+    # fourier_approx (fourier_approx.py:40-49, without its plot) = the two calls above at the sample points
+    np.testing.assert_array_equal(fs.fourier_approx(x, y, case["n"]), fs.fit_func_by_fourier_series_with_real_coeffs(x, ab))
     assert float(fs.fit_func_by_fourier_series_with_real_coeffs(0.25, ab)) == pytest.approx(
         fs.fit_func_by_fourier_series_with_real_coeffs(np.array([0.25]), ab)[0])
 
