@@ -20,7 +20,9 @@ from .models import (
 from .ode_solver import OdeSolver
 from .ivp_fes import IvpFes
 from .ocp_fes import OcpFes, FesShooting, FesNmpcBatch
-from .bioptim_seam import FesIntegrator
+from .bioptim_seam import FesIntegrator, GpuRK4
+from .custom_objectives import CustomObjective
+from .pickle_io import SolutionToPickle
 from .fourier_approx import FourierSeries
 from .identification import (
     DingModelFrequencyForceParameterIdentification,
@@ -29,7 +31,7 @@ from .identification import (
 )
 
 __all__ = [
-    "fes", "hill_coefficients", "FesModel", "ModelMaker", "OdeSolver", "IvpFes", "OcpFes", "FesShooting", "FesNmpcBatch", "FesIntegrator", "FourierSeries",
+    "fes", "hill_coefficients", "FesModel", "ModelMaker", "OdeSolver", "IvpFes", "OcpFes", "FesShooting", "FesNmpcBatch", "FesIntegrator", "GpuRK4", "FourierSeries", "CustomObjective", "SolutionToPickle",
     "DingModelFrequency", "DingModelFrequencyWithFatigue",
     "DingModelPulseWidthFrequency", "DingModelPulseWidthFrequencyWithFatigue",
     "DingModelPulseIntensityFrequency", "DingModelPulseIntensityFrequencyWithFatigue",

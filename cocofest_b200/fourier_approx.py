@@ -86,3 +86,47 @@ def tracking_objective(X, dt, target=None, end_node_target=None, weight=100.0, e
         cost = cost + end_weight * e * e
         grad[-1, force_row] += 2.0 * end_weight * e
     return cost, grad
+
+
+def best_fit_objective(X, dt, target, weight=1.0, force_row=1):
+    """``track_state_from_time_interpolate(..., minimization_type="best fit")`` (custom_objectives.py:43-74): residual
+    ``1 - target / F`` at every node, squared, node weight dt.  Cost [B] and gradient [ns+1, nx, B]."""
+    F = X[:, force_row]
+    t = torch.as_tensor(target, dtype=X.dtype, device=X.device)
+    if t.dim() == 1:
+        t = t[:, None]
+    if t.shape[0] != F.shape[0]:
+        raise ValueError(f"target must have {F.shape[0]} rows (one per node)")
+    r = 1.0 - t / F
+    grad = torch.zeros_like(X)
+    grad[:, force_row] = (2.0 * weight * dt) * r * (t / (F * F))
+    return (weight * dt) * (r * r).sum(dim=0), grad
+
+
+def muscle_fatigue_objective(X_end, a_rest, weight=1.0, a_row=2):
+    """``minimize_overall_muscle_fatigue`` as ``fes_ocp_dynamics.py:675-683`` uses it (Mayer, last node, quadratic, weight 1):
+    ``(sum_m a_rest_m / sum_m A_m(T))^2`` over the muscles of a scenario (custom_objectives.py:77-97).
+
+    X_end [M, nx, B] end states of the M muscles (or [nx, B] for one), a_rest [M] | [M, B].  Cost [B], gradient like X_end."""
+    single = X_end.dim() == 2
+    Xe = X_end[None] if single else X_end
+    ar = torch.as_tensor(a_rest, dtype=Xe.dtype, device=Xe.device).reshape(Xe.shape[0], -1)
+    num = ar.sum(dim=0) if ar.shape[1] > 1 else ar.sum()
+    den = Xe[:, a_row].sum(dim=0)
+    ratio = num / den
+    grad = torch.zeros_like(Xe)
+    grad[:, a_row] = (-2.0 * weight * ratio * ratio / den)[None].expand(Xe.shape[0], -1)
+    return weight * ratio * ratio, (grad[0] if single else grad)
+
+
+def muscle_force_objective(X, dt, weight=1.0, force_row=1):
+    """``minimize_overall_muscle_force_production`` as ``fes_ocp_dynamics.py:685-693`` uses it (Lagrange, all nodes, quadratic,
+    weight 1): ``sum_nodes dt sum_m F_m^2`` (custom_objectives.py:100-117).
+
+    X [M, ns+1, nx, B] node states of the M muscles (or [ns+1, nx, B] for one).  Cost [B], gradient like X."""
+    single = X.dim() == 3
+    Xm = X[None] if single else X
+    F = Xm[:, :, force_row]
+    grad = torch.zeros_like(Xm)
+    grad[:, :, force_row] = (2.0 * weight * dt) * F
+    return (weight * dt) * (F * F).sum(dim=(0, 1)), (grad[0] if single else grad)
